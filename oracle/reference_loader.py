@@ -1,0 +1,42 @@
+"""Oracle (test infrastructure): import the UNMODIFIED reference from /root/reference.
+
+Only usable in the build container (the GPU box has no /root/reference); used by
+tests/golden/make_golden.py to generate fixtures and by CPU tests (skipped when absent) to
+validate the restatements. Method from SURVEY.md 8c: `tritonclient.utils` needs only numpy;
+`image_client.preprocess` imports after stubbing the three transport modules it pulls in.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+REFERENCE_ROOT = "/root/reference"
+_LIB = os.path.join(REFERENCE_ROOT, "src/python/library")
+_IMAGE_CLIENT = os.path.join(REFERENCE_ROOT, "src/python/examples/image_client.py")
+
+
+def available():
+    return os.path.isdir(_LIB) and os.path.isfile(_IMAGE_CLIENT)
+
+
+def reference_utils():
+    if _LIB not in sys.path:
+        sys.path.insert(0, _LIB)
+    import tritonclient.utils as u  # noqa
+    return u
+
+
+def reference_preprocess():
+    reference_utils()
+    for name in ("tritonclient.grpc", "tritonclient.http", "tritonclient.grpc.model_config_pb2"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    mc = sys.modules["tritonclient.grpc.model_config_pb2"]
+    if not hasattr(mc, "ModelInput"):
+        mi = types.SimpleNamespace(FORMAT_NONE=0, FORMAT_NHWC=1, FORMAT_NCHW=2)
+        mc.ModelInput = mi
+    sys.modules["tritonclient.grpc"].model_config_pb2 = mc
+    spec = importlib.util.spec_from_file_location("_ref_image_client", _IMAGE_CLIENT)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.preprocess

@@ -1,0 +1,142 @@
+"""Seeded input recipes shared by make_golden.py (which runs the reference) and the tests (which
+do not need it). Recipes follow SURVEY.md 8c/8d."""
+import numpy as np
+
+NHWC, NCHW = 1, 2  # ModelInput.Format values used at image_client.py:185
+
+
+def _case(name, seed, W, H, fmt, dtype, scaling, c=3, w=224, h=224, kind="uniform", mode="RGB"):
+    return {"name": name, "seed": seed, "W": W, "H": H, "format": fmt, "dtype": dtype,
+            "scaling": scaling, "c": c, "w": w, "h": h, "kind": kind, "mode": mode}
+
+
+PREPROCESS_CASES = [
+    # the six SURVEY.md 8c goldens
+    _case("s0_640x480_nchw_f32_inception", 0, 640, 480, NCHW, "FP32", "INCEPTION"),
+    _case("s1_1080p_nchw_f32_vgg", 1, 1920, 1080, NCHW, "FP32", "VGG"),
+    _case("s2_1080p_nhwc_f16_inception", 2, 1920, 1080, NHWC, "FP16", "INCEPTION"),
+    _case("s3_150x100_nhwc_f16_none_upscale", 3, 150, 100, NHWC, "FP16", "NONE"),
+    _case("s4_224_identity_nchw_f32_none", 4, 224, 224, NCHW, "FP32", "NONE"),
+    _case("s5_500x375_nhwc_f32_vgg", 5, 500, 375, NHWC, "FP32", "VGG"),
+    # more geometries (cfg5's size menu and awkward ones)
+    _case("s6_800x600", 6, 800, 600, NHWC, "FP16", "INCEPTION"),
+    _case("s7_1024x768", 7, 1024, 768, NCHW, "FP32", "VGG"),
+    _case("s8_1280x720", 8, 1280, 720, NHWC, "FP16", "INCEPTION"),
+    _case("s9_375x500", 9, 375, 500, NCHW, "FP32", "INCEPTION"),
+    _case("s10_4k", 10, 3840, 2160, NCHW, "FP32", "VGG"),
+    _case("s11_223x225", 11, 223, 225, NHWC, "FP32", "NONE"),
+    _case("s12_300x224_w_only", 12, 300, 224, NCHW, "FP32", "NONE"),
+    _case("s13_224x300_h_only", 13, 224, 300, NCHW, "FP32", "NONE"),
+    _case("s14_1x1", 14, 1, 1, NHWC, "FP32", "INCEPTION"),
+    _case("s15_2x3", 15, 2, 3, NCHW, "FP32", "VGG"),
+    _case("s16_7x1000_tall_vfirst", 16, 7, 1000, NHWC, "FP32", "NONE"),
+    _case("s17_1000x7_wide", 17, 1000, 7, NHWC, "FP32", "NONE"),
+    _case("s18_9x1000_vfirst", 18, 9, 1000, NCHW, "FP32", "NONE"),
+    _case("s19_10x1000_hfirst", 19, 10, 1000, NCHW, "FP32", "NONE"),
+    _case("s20_3x301_vfirst", 20, 3, 301, NCHW, "FP32", "NONE"),
+    _case("s21_4000x3000", 21, 4000, 3000, NHWC, "FP16", "VGG"),
+    _case("s22_53x37_to_299", 22, 53, 37, NCHW, "FP32", "INCEPTION", w=299, h=299),
+    _case("s23_640x480_to_299", 23, 640, 480, NHWC, "FP32", "INCEPTION", w=299, h=299),
+    _case("s24_odd_out_17x9", 24, 640, 480, NCHW, "FP32", "VGG", w=17, h=9),
+    # grayscale target (c == 1): RGB -> L conversion before the resize
+    _case("s25_rgb_to_l_640x480", 25, 640, 480, NCHW, "FP32", "VGG", c=1),
+    _case("s26_rgb_to_l_1080p_f16", 26, 1920, 1080, NHWC, "FP16", "INCEPTION", c=1),
+    # other source modes handled by convert()
+    _case("s27_l_to_rgb", 27, 320, 240, NCHW, "FP32", "INCEPTION", mode="L"),
+    _case("s28_rgba_to_rgb", 28, 320, 240, NHWC, "FP32", "VGG", mode="RGBA"),
+    _case("s29_l_to_l", 29, 320, 240, NHWC, "FP16", "NONE", c=1, mode="L"),
+    _case("s30_rgba_to_l", 30, 123, 77, NCHW, "FP32", "NONE", c=1, mode="RGBA"),
+    # structured images exercising rounding edges
+    _case("z_all0", 0, 640, 480, NCHW, "FP32", "INCEPTION", kind="zeros"),
+    _case("z_all255", 0, 640, 480, NCHW, "FP32", "INCEPTION", kind="ones255"),
+    _case("z_checker", 0, 641, 479, NHWC, "FP16", "VGG", kind="checker"),
+    _case("z_xgrad", 0, 1920, 1080, NCHW, "FP32", "NONE", kind="xgrad"),
+    _case("z_ygrad", 0, 1280, 720, NCHW, "FP32", "NONE", kind="ygrad"),
+    # numpy promotion oddities
+    _case("d_uint8_inception_f64", 31, 640, 480, NCHW, "UINT8", "INCEPTION"),
+    _case("d_uint8_vgg_wrap", 32, 640, 480, NHWC, "UINT8", "VGG"),
+    _case("d_int32_none", 33, 320, 240, NCHW, "INT32", "NONE"),
+    _case("d_fp64_vgg", 34, 320, 240, NHWC, "FP64", "VGG"),
+    _case("d_int8_vgg", 35, 320, 240, NHWC, "INT8", "VGG"),
+    _case("d_uint16_inception", 36, 320, 240, NHWC, "UINT16", "INCEPTION"),
+    # tiny outputs stored in full (preprocess_small.npz)
+    _case("t_small_64x48_to_8x8", 40, 64, 48, NCHW, "FP32", "INCEPTION", w=8, h=8),
+    _case("t_small_up_5x4_to_16x12", 41, 5, 4, NHWC, "FP16", "VGG", w=16, h=12),
+    _case("t_small_31x17_to_13x11_l", 42, 31, 17, NCHW, "FP32", "VGG", c=1, w=13, h=11),
+]
+
+
+def make_image(case):
+    """uint8 source array: [H, W, 3] for RGB, [H, W] for L, [H, W, 4] for RGBA."""
+    H, W = case["H"], case["W"]
+    nch = {"RGB": 3, "L": 1, "RGBA": 4}[case["mode"]]
+    kind = case["kind"]
+    if kind == "uniform":
+        a = np.random.default_rng(case["seed"]).integers(0, 256, (H, W, nch), dtype=np.uint8)
+    elif kind == "zeros":
+        a = np.zeros((H, W, nch), dtype=np.uint8)
+    elif kind == "ones255":
+        a = np.full((H, W, nch), 255, dtype=np.uint8)
+    elif kind == "checker":
+        yy, xx = np.mgrid[0:H, 0:W]
+        a = (((yy + xx) & 1) * 255).astype(np.uint8)[:, :, None].repeat(nch, axis=2)
+    elif kind == "xgrad":
+        a = ((np.arange(W) * 255) // max(W - 1, 1)).astype(np.uint8)[None, :, None].repeat(H, 0).repeat(nch, 2)
+    elif kind == "ygrad":
+        a = ((np.arange(H) * 255) // max(H - 1, 1)).astype(np.uint8)[:, None, None].repeat(W, 1).repeat(nch, 2)
+    else:
+        raise ValueError(kind)
+    a = np.ascontiguousarray(a)
+    if nch == 1:
+        a = a[:, :, 0]
+    return a
+
+
+def to_pil(src, case):
+    from PIL import Image
+
+    return Image.fromarray(src, case["mode"])
+
+
+# ---- BYTES ------------------------------------------------------------------------------------
+GBYTES_N = [16, 1000, 1_000_000]
+
+
+def gbytes(n, seed=42, max_len=256):
+    rng = np.random.default_rng(seed)
+    lens = rng.integers(0, max_len + 1, n, dtype=np.int64)
+    blob = rng.integers(0, 256, int(lens.sum()), dtype=np.uint8)
+    return blob, lens
+
+
+def to_object_array(blob, lens):
+    off = np.zeros(len(lens) + 1, dtype=np.int64)
+    np.cumsum(lens, out=off[1:])
+    b = blob.tobytes()
+    arr = np.empty(len(lens), dtype=np.object_)
+    for i in range(len(lens)):
+        arr[i] = b[off[i]:off[i + 1]]
+    return arr
+
+
+def object_cases():
+    """Inputs whose per-element normalisation is non-trivial (utils/__init__.py:229-239)."""
+    c = {}
+    c["bytes_1d"] = np.array([b"a", b"", b"bcd", b"\x00\x01\x00"], dtype=np.object_)
+    c["str_elems"] = np.array(["he\x00llo", "wörld", ""], dtype=np.object_)
+    c["mixed_objs"] = np.array([b"x", "y", 12, None, 3.5, np.bytes_(b"zz")], dtype=np.object_)
+    c["bytes_2d_fortran"] = np.asfortranarray(
+        np.array([[b"00", b"01", b"02"], [b"10", b"11", b"12"]], dtype=np.object_))
+    c["bytes_view_T"] = np.array([[b"00", b"01", b"02"], [b"10", b"11", b"12"]], dtype=np.object_).T
+    c["np_bytes_S4_trailing_nul"] = np.array([b"\x00\x01\x02\x03", b"ab\x00\x00", b"\x00\x00\x00\x00", b"abcd"],
+                                             dtype=np.bytes_)
+    c["np_bytes_S_2d"] = np.array([[b"a", b"bcd"], [b"", b"ef"]], dtype="S3")
+    c["empty_obj"] = np.empty((0,), dtype=np.object_)
+    c["empty_2d"] = np.empty((3, 0), dtype=np.object_)
+    c["zero_d"] = np.array(b"solo", dtype=np.object_)
+    # reference usage vectors
+    c["ref_test_numpy_bytes"] = np.array([str(x).encode("utf-8") for x in range(16)], dtype=np.object_)
+    c["ref_string_infer_object"] = np.array([["he\x00llo"] * 16], dtype=np.object_)
+    c["ref_string_infer_bytes_"] = np.array([[b"\x00\x01\x02\x03"] * 16], dtype=np.bytes_)
+    c["ref_cc_client_test"] = np.array([b"\x01\x7f", b"\x02\x7f"], dtype=np.object_)
+    return c

@@ -1,0 +1,87 @@
+#!/usr/bin/env python
+"""Generates tests/golden/*.json|*.npz by running the UNMODIFIED reference imported from
+/root/reference (only possible in the build container; the GPU box has no /root/reference).
+
+    python tests/golden/make_golden.py
+
+Inputs are seeded numpy generators so that every test can rebuild them without the reference;
+outputs are stored as sha256 hex digests (large cases) or as full arrays (tiny cases).
+Recorded environment: Pillow / numpy versions of the generating container (Pillow's resampler is
+third-party and unpinned by the reference; see oracle/__init__.py).
+"""
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from oracle import reference_loader as rl  # noqa: E402
+from tests.golden import cases  # noqa: E402
+
+
+def sha(b):
+    return hashlib.sha256(b).hexdigest()
+
+
+def main():
+    import PIL
+    from PIL import Image
+
+    assert rl.available(), "needs /root/reference"
+    pre = rl.reference_preprocess()
+    utils = rl.reference_utils()
+    env = {"pillow": PIL.__version__, "numpy": np.__version__}
+
+    # ---- preprocess -------------------------------------------------------------------------
+    gold = {"env": env, "cases": []}
+    small = {}
+    for case in cases.PREPROCESS_CASES:
+        src = cases.make_image(case)
+        img = cases.to_pil(src, case)
+        out = pre(img, case["format"], case["dtype"], case["c"], case["h"], case["w"],
+                  case["scaling"], "grpc")
+        outc = np.ascontiguousarray(out)
+        rec = dict(case)
+        rec["src_sha256"] = sha(np.ascontiguousarray(src).tobytes())
+        rec["out_sha256"] = sha(outc.tobytes())
+        rec["out_dtype"] = str(outc.dtype)
+        rec["out_shape"] = list(outc.shape)
+        conv = img.convert("L" if case["c"] == 1 else "RGB")
+        u8 = np.array(conv.resize((case["w"], case["h"]), Image.BILINEAR))
+        rec["u8_sha256"] = sha(np.ascontiguousarray(u8).tobytes())
+        gold["cases"].append(rec)
+        if outc.nbytes <= 16384:
+            small[case["name"]] = outc
+    with open(os.path.join(HERE, "preprocess_golden.json"), "w") as f:
+        json.dump(gold, f, indent=1)
+    np.savez_compressed(os.path.join(HERE, "preprocess_small.npz"), **small)
+
+    # ---- BYTES ------------------------------------------------------------------------------
+    bg = {"env": env, "gbytes": [], "objects": []}
+    for n in cases.GBYTES_N:
+        blob, lens = cases.gbytes(n)
+        arr = cases.to_object_array(blob, lens)
+        ser = utils.serialize_byte_tensor(arr).item()
+        back = utils.deserialize_bytes_tensor(ser)
+        assert np.array_equal(back, arr)
+        bg["gbytes"].append({"n": n, "seed": 42, "payload_bytes": int(lens.sum()),
+                             "serialized_bytes": len(ser), "blob_sha256": sha(blob.tobytes()),
+                             "serialized_sha256": sha(ser)})
+    # odd object/bytes_ inputs: what the reference's per-element normalisation yields
+    for name, arr in cases.object_cases().items():
+        r = utils.serialize_byte_tensor(arr)
+        ser = r.item() if r.size > 0 else b""
+        bg["objects"].append({"name": name, "serialized_hex": ser.hex(),
+                              "result_shape": list(r.shape), "result_dtype": str(r.dtype)})
+    with open(os.path.join(HERE, "bytes_golden.json"), "w") as f:
+        json.dump(bg, f, indent=1)
+    print("wrote goldens:", len(gold["cases"]), "preprocess cases,", len(bg["gbytes"]), "gbytes,",
+          len(bg["objects"]), "object cases")
+
+
+if __name__ == "__main__":
+    main()
