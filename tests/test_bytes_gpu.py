@@ -1,0 +1,190 @@
+"""GPU parity tests for the BYTES codec through the C ABI: bit-exact against the goldens
+generated from the unmodified reference, the reference's known-answer vectors, and the oracle."""
+import hashlib
+import json
+import os
+import struct
+
+import numpy as np
+import pytest
+
+from oracle import bytes_codec as bc
+from oracle import clib
+from tests.golden import cases
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+BYT = json.load(open(os.path.join(GOLD, "bytes_golden.json")))
+
+
+def sha(b):
+    return hashlib.sha256(b).hexdigest()
+
+
+@pytest.mark.parametrize("rec", BYT["objects"], ids=[o["name"] for o in BYT["objects"]])
+def test_serialize_dropin_object_cases(rec):
+    from triton_client_b200 import utils as u
+
+    arr = cases.object_cases()[rec["name"]]
+    r = u.serialize_byte_tensor(arr)
+    assert list(r.shape) == rec["result_shape"] and str(r.dtype) == rec["result_dtype"]
+    ser = r.item() if r.size > 0 else b""
+    assert ser.hex() == rec["serialized_hex"]
+    if ser:
+        assert u.serialized_byte_size(r) == len(ser)
+        back = u.deserialize_bytes_tensor(ser)
+        assert back.dtype == np.object_ and back.ndim == 1
+        assert list(back) == bc.deserialize_stream(ser)
+
+
+def test_known_answer_cc_client_test():
+    # /root/reference/src/c++/tests/cc_client_test.cc:1929-1953, 2140-2153
+    from triton_client_b200 import utils as u
+
+    wire = bytes([2, 0, 0, 0, 1, 127, 2, 0, 0, 0, 2, 127])
+    assert u.serialize_byte_tensor(np.array([b"\x01\x7f", b"\x02\x7f"], dtype=np.object_)).item() == wire
+    assert list(u.deserialize_bytes_tensor(wire)) == [b"\x01\x7f", b"\x02\x7f"]
+
+
+@pytest.mark.parametrize("rec", BYT["gbytes"], ids=[str(g["n"]) for g in BYT["gbytes"]])
+def test_gbytes_device_path_bit_exact(rec):
+    import torch
+
+    from triton_client_b200 import utils as u
+
+    blob, lens = cases.gbytes(rec["n"])
+    d_blob = torch.from_numpy(blob).cuda()
+    for ldt in (np.int32, np.int64):
+        d_lens = torch.from_numpy(lens.astype(ldt)).cuda()
+        out, total = u.serialize_to_device(d_blob, d_lens)
+        assert total == rec["serialized_bytes"]
+        ser = out[:total].cpu().numpy()
+        assert sha(ser.tobytes()) == rec["serialized_sha256"]
+    offsets, payload = u.deserialize_from_device(out, total)
+    assert offsets.numel() == rec["n"] + 1
+    assert np.array_equal(np.diff(offsets.cpu().numpy()), lens)
+    assert np.array_equal(payload.cpu().numpy(), blob)
+    # limited decode (get_contents_as_numpy semantics): first m elements only
+    m = rec["n"] // 3 + 1
+    off2, pay2 = u.deserialize_from_device(out, total, max_elements=m)
+    assert off2.numel() == m + 1
+    assert np.array_equal(off2.cpu().numpy(), offsets.cpu().numpy()[: m + 1])
+    assert np.array_equal(pay2.cpu().numpy(), blob[: int(off2[-1])])
+
+
+def test_serialize_dropin_gbytes_1000_and_unaligned_destination():
+    import torch
+
+    from triton_client_b200 import utils as u
+
+    blob, lens = cases.gbytes(1000)
+    arr = cases.to_object_array(blob, lens)
+    ser = u.serialize_byte_tensor(arr).item()
+    assert sha(ser) == BYT["gbytes"][1]["serialized_sha256"]
+    back = u.deserialize_bytes_tensor(ser)
+    assert np.array_equal(back, arr)
+    # arbitrary destination / source misalignment exercises the byte paths
+    d_blob_pad = torch.zeros(blob.size + 16, dtype=torch.uint8, device="cuda")
+    d_lens = torch.from_numpy(lens).cuda()
+    for src_mis in (0, 1, 2, 3, 5):
+        d_blob = d_blob_pad[src_mis: src_mis + blob.size]
+        d_blob.copy_(torch.from_numpy(blob))
+        for dst_mis in (0, 1, 4, 7, 13):
+            out = torch.full((len(ser) + 64,), 0xAB, dtype=torch.uint8, device="cuda")
+            _, total = u.serialize_to_device(d_blob, d_lens, out, dst_mis)
+            h = out.cpu().numpy()
+            assert total == len(ser)
+            assert h[dst_mis: dst_mis + total].tobytes() == ser, (src_mis, dst_mis)
+            assert (h[:dst_mis] == 0xAB).all() and (h[dst_mis + total:] == 0xAB).all()
+            offs, pay = u.deserialize_from_device(out, total, stream_offset=dst_mis)
+            assert np.array_equal(pay.cpu().numpy(), blob)
+
+
+def _roundtrip(lens, payload_kind="random", seed=0):
+    import torch
+
+    from triton_client_b200 import utils as u
+
+    lens = np.asarray(lens, dtype=np.int64)
+    rng = np.random.default_rng(seed)
+    total = int(lens.sum())
+    if payload_kind == "random":
+        blob = rng.integers(0, 256, total, dtype=np.uint8)
+    elif payload_kind == "zeros":
+        blob = np.zeros(total, dtype=np.uint8)
+    elif payload_kind == "ascii":
+        blob = rng.integers(0x20, 0x7F, total, dtype=np.uint8)
+    elif payload_kind == "small_ints":  # payloads that look like plausible length prefixes
+        blob = np.zeros(total, dtype=np.uint8)
+        blob[::4] = rng.integers(0, 40, blob[::4].size, dtype=np.uint8)
+    ref = clib.bytes_serialize(blob, lens)
+    out, tot = u.serialize_to_device(torch.from_numpy(blob).cuda(), torch.from_numpy(lens).cuda())
+    assert tot == ref.size
+    assert np.array_equal(out[:tot].cpu().numpy(), ref)
+    offsets, payload = u.deserialize_from_device(out, tot)
+    assert np.array_equal(np.diff(offsets.cpu().numpy()), lens)
+    assert np.array_equal(payload.cpu().numpy(), blob)
+
+
+@pytest.mark.parametrize("kind", ["random", "zeros", "ascii", "small_ints"])
+def test_roundtrip_payload_kinds(kind):
+    rng = np.random.default_rng(3)
+    _roundtrip(rng.integers(0, 257, 20000), kind, seed=4)
+
+
+def test_roundtrip_edge_lengths():
+    _roundtrip([0])
+    _roundtrip([1])
+    _roundtrip([0] * 5000)                       # prefixes only
+    _roundtrip([3, 0, 0, 1, 0, 2] * 1000)        # many elements per 16-byte chunk
+    _roundtrip([100000, 5, 70000, 0, 9000])      # elements far longer than a deserialise chunk
+    _roundtrip([1 << 20])                        # a single 1 MiB element
+    _roundtrip(np.full(3000, 600))               # longer than the look-behind window (sweep path)
+    _roundtrip(np.random.default_rng(1).integers(0, 5000, 3000))
+    _roundtrip([2] * 40000, "zeros")             # more headers per chunk than the per-chunk list holds
+
+
+def test_truncated_streams_raise_struct_error():
+    from triton_client_b200 import utils as u
+
+    good = bc.serialize_elements(np.array([b"abc", b"de", b"f" * 9000, b""], dtype=np.object_))
+    for cut in (1, 2, 3, 5, 6, 8, 12, 13, 5000, len(good) - 4, len(good) - 1):
+        with pytest.raises(struct.error):
+            u.deserialize_bytes_tensor(good[:cut])
+    assert len(u.deserialize_bytes_tensor(good)) == 4
+    assert u.deserialize_bytes_tensor(b"").shape == (0,)
+    # a header that claims more than the buffer holds
+    with pytest.raises(struct.error):
+        u.deserialize_bytes_tensor(struct.pack("<I", 100) + b"x" * 10)
+
+
+def test_serialize_into_region_and_capacity_error():
+    import torch
+
+    from triton_client_b200 import _lib
+    from triton_client_b200 import utils as u
+    from triton_client_b200.utils import cuda_shared_memory as cudashm
+
+    blob, lens = cases.gbytes(1000)
+    arr = cases.to_object_array(blob, lens)
+    ref = bc.serialize_elements(arr)
+    region = cudashm.create_shared_memory_region("ser", len(ref) + 100, 0)
+    try:
+        n = u.serialize_byte_tensor_to(region, arr, out_offset=32)
+        assert n == len(ref)
+        got = cudashm.get_contents_as_numpy(region, np.uint8, [len(ref)], offset=32)
+        assert got.tobytes() == ref
+        back = cudashm.get_contents_as_numpy(region, np.object_, [10, 100], offset=32)
+        assert back.shape == (10, 100) and np.array_equal(back.reshape(-1), arr)
+        # S<k> arrays: trailing NULs stripped on the device
+        s_arr = np.array([b"\x00\x01\x02\x03", b"ab\x00\x00", b"\x00\x00\x00\x00", b"abcd"] * 300, dtype=np.bytes_)
+        n2 = u.serialize_byte_tensor_to(region, s_arr)
+        got2 = cudashm.get_contents_as_numpy(region, np.uint8, [n2])
+        assert got2.tobytes() == bc.serialize_elements(s_arr)
+        small = torch.zeros(100, dtype=torch.uint8, device="cuda")
+        with pytest.raises(_lib.TcbError) as ei:
+            u.serialize_to_device(torch.from_numpy(blob).cuda(), torch.from_numpy(lens).cuda(), small)
+        assert ei.value.code == _lib.TCB_ERR_OUT_OF_RANGE
+    finally:
+        cudashm.destroy_shared_memory_region(region)

@@ -1,0 +1,149 @@
+"""GPU parity tests for the preprocess path: the drop-in ``preprocess`` and the batched
+region-writing form, through the C ABI, against (a) the goldens generated from the unmodified
+reference and (b) the oracle on the same seeded inputs. Bar: bit-exact (the north_star tolerance
+of <= 1e-2 after scaling is met with zero difference)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import clib
+from oracle import pil_bilinear as pb
+from tests.golden import cases
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+PRE = json.load(open(os.path.join(GOLD, "preprocess_golden.json")))
+SMALL = np.load(os.path.join(GOLD, "preprocess_small.npz"))
+
+
+def sha(b):
+    return hashlib.sha256(b).hexdigest()
+
+
+def oracle_preprocess(src, c, h, w, fmt, dtype, scaling):
+    src = src[:, :, None] if src.ndim == 2 else src
+    u8 = clib.resize_bilinear_u8(pb.convert_u8(src, c), w, h)
+    lut = pb.scaling_lut(dtype, c, scaling)
+    out = np.empty(u8.shape, dtype=lut.dtype)
+    for ch in range(c):
+        out[:, :, ch] = lut[ch][u8[:, :, ch]]
+    return np.ascontiguousarray(np.transpose(out, (2, 0, 1)) if fmt == 2 else out)
+
+
+@pytest.mark.parametrize("rec", PRE["cases"], ids=[c["name"] for c in PRE["cases"]])
+def test_preprocess_dropin_matches_reference_golden(rec):
+    from triton_client_b200.image_client import preprocess
+
+    src = cases.make_image(rec)
+    img = cases.to_pil(src, rec)
+    out = preprocess(img, rec["format"], rec["dtype"], rec["c"], rec["h"], rec["w"], rec["scaling"], "grpc")
+    assert str(out.dtype) == rec["out_dtype"]
+    assert list(out.shape) == rec["out_shape"]
+    outc = np.ascontiguousarray(out)
+    if sha(outc.tobytes()) != rec["out_sha256"]:
+        ref = oracle_preprocess(src, rec["c"], rec["h"], rec["w"], rec["format"], rec["dtype"], rec["scaling"])
+        diff = np.abs(outc.astype(np.float64) - ref.astype(np.float64))
+        raise AssertionError("mismatch vs golden: max abs diff %g at %d positions" % (diff.max(), (diff > 0).sum()))
+    if rec["name"] in SMALL.files:
+        assert np.array_equal(outc, SMALL[rec["name"]])
+
+
+def _batch_case(sizes, fmt, dtype, c, scaling, h=224, w=224, seed=0, path=0):
+    import torch
+
+    from triton_client_b200.image_client import PreprocessPlan
+    from triton_client_b200.utils import cuda_shared_memory as cudashm
+
+    rng = np.random.default_rng(seed)
+    srcs = [rng.integers(0, 256, (H, W, ch), dtype=np.uint8) for (W, H, ch) in sizes]
+    d_imgs = [torch.from_numpy(s).cuda() for s in srcs]
+    plan = PreprocessPlan(sizes, fmt, dtype, c, h, w, scaling, device=0, path=path)
+    nbytes = plan.n * plan.out_bytes_per_image
+    region = cudashm.create_shared_memory_region("pre_batch", nbytes + 64, 0)
+    try:
+        plan.run([t.data_ptr() for t in d_imgs], region._base_addr + 64, nbytes)
+        torch.cuda.synchronize()
+        got = cudashm.get_contents_as_numpy(region, np.uint8, [nbytes + 64])[64:]
+        got = got.view(plan.out_dtype).reshape(plan.out_shape)
+        for i, s in enumerate(srcs):
+            ref = oracle_preprocess(s, c, h, w, fmt, dtype, scaling)
+            assert np.array_equal(got[i], ref), "image %d %s differs" % (i, sizes[i])
+        return plan.info()
+    finally:
+        plan.close()
+        cudashm.destroy_shared_memory_region(region)
+
+
+def test_batch_mixed_resolution_into_region_nhwc_f16():
+    # cfg5's size menu (upscale + identity included), sharded into one region at an offset
+    menu = [(640, 480), (800, 600), (1024, 768), (1280, 720), (1920, 1080), (500, 375), (375, 500),
+            (224, 224), (150, 100)]
+    sizes = [(w, h, 3) for (w, h) in menu] * 2
+    _batch_case(sizes, 1, "FP16", 3, "INCEPTION", seed=1234)
+
+
+def test_batch_same_size_nchw_f32_vgg():
+    _batch_case([(1920, 1080, 3)] * 6, 2, "FP32", 3, "VGG", seed=1000)
+
+
+def test_batch_two_pass_path_forced():
+    _batch_case([(640, 480, 3), (1920, 1080, 3), (7, 1000, 3), (224, 300, 3), (300, 224, 3), (224, 224, 3)],
+                2, "FP32", 3, "INCEPTION", seed=5, path=1)
+
+
+def test_batch_gray_and_rgba_sources():
+    _batch_case([(640, 480, 4), (320, 240, 1), (641, 479, 3)], 2, "FP32", 1, "VGG", seed=6)
+    _batch_case([(640, 480, 4), (320, 240, 1), (641, 479, 3)], 1, "FP16", 3, "NONE", seed=7)
+
+
+def test_batch_other_targets():
+    _batch_case([(640, 480, 3), (1920, 1080, 3)], 2, "FP32", 3, "INCEPTION", h=299, w=299, seed=8)
+    _batch_case([(640, 480, 3), (100, 50, 3)], 1, "UINT8", 3, "NONE", h=17, w=31, seed=9)
+    _batch_case([(64, 64, 3)], 2, "FP64", 3, "VGG", h=512, w=384, seed=10)
+
+
+def test_plan_rejects_small_output_and_bad_geometry():
+    import torch
+
+    from triton_client_b200 import _lib
+    from triton_client_b200.image_client import PreprocessPlan
+
+    plan = PreprocessPlan([(64, 48, 3)], 2, "FP32", 3, 8, 8, "NONE", device=0)
+    src = torch.zeros((48, 64, 3), dtype=torch.uint8, device="cuda")
+    dst = torch.zeros(8 * 8 * 3, dtype=torch.float32, device="cuda")
+    with pytest.raises(_lib.TcbError) as ei:
+        plan.run([src.data_ptr()], dst.data_ptr(), 8 * 8 * 3 * 4 - 1)
+    assert ei.value.code == _lib.TCB_ERR_OUT_OF_RANGE
+    plan.run([src.data_ptr()], dst.data_ptr(), 8 * 8 * 3 * 4)
+    torch.cuda.synchronize()
+    assert float(dst.abs().sum()) == 0.0
+    plan.close()
+
+
+def test_full_size_properties_cfg3():
+    """cfg3 at full size (256 x 1080p -> 224^2 f32 NCHW VGG): checked through properties that do
+    not need the oracle on every image: identical images give identical outputs, a constant image
+    maps to the constant LUT value, and a strided sample of images equals the oracle."""
+    import torch
+
+    from triton_client_b200.image_client import preprocess_batch
+
+    n = 256
+    g = torch.Generator(device="cuda").manual_seed(1000)
+    batch = torch.randint(0, 256, (n, 1080, 1920, 3), dtype=torch.uint8, device="cuda", generator=g)
+    batch[7] = batch[3]
+    batch[11] = 200
+    out, plan = preprocess_batch(batch, 2, "FP32", 3, 224, 224, "VGG")
+    assert out.shape == (n, 3, 224, 224)
+    assert torch.equal(out[7], out[3])
+    lut = pb.scaling_lut("FP32", 3, "VGG")
+    for ch in range(3):
+        assert torch.all(out[11, ch] == float(lut[ch, 200]))
+    for i in (0, 100, 255):
+        ref = oracle_preprocess(batch[i].cpu().numpy(), 3, 224, 224, 2, "FP32", "VGG")
+        assert np.array_equal(out[i].cpu().numpy(), ref)
+    plan.close()

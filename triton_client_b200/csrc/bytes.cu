@@ -1,0 +1,759 @@
+// BYTES tensor (de)serialisation kernels behind the C ABI (include/tcb200.h).
+//
+// Wire format (/root/reference/src/python/library/tritonclient/utils/__init__.py:193-276): per
+// element, in C order, a little-endian uint32 length followed by the payload bytes.
+//
+// Serialise  (replaces the np.nditer + struct.pack + b"".join loop, utils/__init__.py:229-242):
+//   one kernel; per tile of 1024 elements: lengths -> warp-shuffle block scan -> decoupled
+//   look-back for the tile's global payload offset -> coalesced scatter of prefixes + payload.
+//   Output-centric: every thread builds 16 aligned destination bytes at a time. Because element i
+//   starts at src_off[i] + 4*i, payload bytes move by a multiple of 4, so interior words are
+//   plain aligned 32-bit loads.
+// Deserialise (replaces the unpack_from loop, utils/__init__.py:270-275 and
+//   cuda_shared_memory/__init__.py:312-318): the pointer chase is cut into 8 KiB chunks. Each
+//   chunk guesses its entry header by chasing from every byte of a 512-byte look-behind window
+//   and voting, then chases its own chain; a verify pass checks entry[k+1] == exit[k] for every
+//   chunk, which makes the result exact; any mismatch (elements longer than the window,
+//   adversarial payloads) is repaired by a sequential sweep. A scan of per-chunk counts gives
+//   element indices; payloads are then gathered with the same output-centric copy.
+#include "common.cuh"
+
+namespace tcb {
+
+// =================================================================================================
+// small device helpers
+// =================================================================================================
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ldg_u32(const uint8_t* p) {
+  return __ldg(reinterpret_cast<const uint32_t*>(p));
+}
+__device__ __forceinline__ void st_v4(uint8_t* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d)
+               : "memory");
+}
+
+// status word of the look-back scan: flag in bits 63..62, value in bits 61..0
+constexpr unsigned long long kFlagAgg = 1ull << 62;
+constexpr unsigned long long kFlagInc = 2ull << 62;
+constexpr unsigned long long kValMask = (1ull << 62) - 1;
+constexpr unsigned int kSpinLimit = 1u << 24;  // bounded: a lost tile becomes an error, not a hang
+
+// workspace header (in 64-bit words)
+enum : int { WS_TICKET = 0, WS_ERROR = 1, WS_TOTAL = 2, WS_HEADER_WORDS = 8 };
+enum : unsigned long long { ERR_NONE = 0, ERR_SPIN = 1, ERR_CAPACITY = 2 };
+
+// =================================================================================================
+// serialise
+// =================================================================================================
+constexpr int kSerThreads = 256;
+constexpr int kSerItems = 4;
+constexpr int kSerTile = kSerThreads * kSerItems;
+
+// Exclusive look-back over tile aggregates (single-pass scan, Merrill & Garland style). Called by
+// warp 0 of the CTA that owns `tile`; tiles are handed out by an atomic ticket so every
+// predecessor is already running. Returns the exclusive prefix in all lanes.
+__device__ unsigned long long lookback_exclusive(unsigned long long* status, unsigned int tile,
+                                                 unsigned long long aggregate,
+                                                 unsigned long long* ws) {
+  const int lane = threadIdx.x & 31;
+  if (lane == 0) st_relaxed_u64(&status[tile], (tile == 0 ? kFlagInc : kFlagAgg) | aggregate);
+  unsigned long long exclusive = 0;
+  if (tile == 0) return 0;
+  long long look = (long long)tile - 1;
+  while (true) {
+    const long long idx = look - lane;
+    unsigned long long st = kFlagInc;  // virtual predecessors of tile 0: inclusive 0
+    if (idx >= 0) {
+      unsigned int spins = 0;
+      st = ld_relaxed_u64(&status[idx]);
+      while ((st >> 62) == 0) {
+        if (++spins > kSpinLimit) {
+          atomicMax(&ws[WS_ERROR], (unsigned long long)ERR_SPIN);
+          st = kFlagInc;
+          break;
+        }
+        __nanosleep(20);
+        st = ld_relaxed_u64(&status[idx]);
+      }
+    }
+    const unsigned inc_mask = __ballot_sync(0xffffffffu, (st >> 62) == 2);
+    unsigned long long v = st & kValMask;
+    if (inc_mask) {
+      const int first = __ffs(inc_mask) - 1;  // nearest predecessor that knows its inclusive prefix
+      if (lane > first) v = 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    exclusive += v;
+    if (inc_mask) break;
+    look -= 32;
+  }
+  if (lane == 0) st_relaxed_u64(&status[tile], kFlagInc | (exclusive + aggregate));
+  return exclusive;
+}
+
+// Copies the payload of the tile's elements between "blob space" (payloads back to back) and
+// "stream space" (each element preceded by its 4-byte length). TO_STREAM = serialise direction.
+//   s_off[e]  : blob offset of tile element e relative to the tile's first element (e in 0..nE)
+//   blob0     : global blob offset of the tile's first element
+//   e0        : global index of the tile's first element
+// Output-centric: 16 aligned output bytes per thread per step, vector store for full chunks.
+template <bool TO_STREAM, bool WORD_OK>
+__device__ __forceinline__ void move_tile(const unsigned long long* s_off, int nE,
+                                          unsigned long long blob0, unsigned long long e0,
+                                          const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                          unsigned long long dst_capacity) {
+  // output coordinates are shifted by `mis` so that multiples of 16 are 16-byte aligned addresses
+  const unsigned long long mis = reinterpret_cast<uintptr_t>(dst) & 15;
+  uint8_t* vd = dst - mis;
+  // tile output range [o0, o1) in unshifted output offsets
+  const unsigned long long o0 = TO_STREAM ? blob0 + 4 * e0 : blob0;
+  const unsigned long long o1 = TO_STREAM ? blob0 + s_off[nE] + 4 * (e0 + nE) : blob0 + s_off[nE];
+  const unsigned long long lim = min(o1, dst_capacity) + mis;
+  const unsigned long long A = o0 + mis;
+  if (lim <= A) return;
+  const unsigned long long q0 = A >> 4, q1 = (lim + 15) >> 4;
+  for (unsigned long long q = q0 + threadIdx.x; q < q1; q += blockDim.x) {
+    const unsigned long long cb = q << 4;
+    const unsigned long long a = max(cb, A), b = min(cb + 16, lim);
+    // element containing output byte a: largest e with start(e) <= a
+    const unsigned long long rel = a - A;
+    int lo = 0, hi = nE;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      const unsigned long long st = TO_STREAM ? s_off[mid] + 4ull * mid : s_off[mid];
+      if (st <= rel) lo = mid; else hi = mid;
+    }
+    int e = lo;
+    // element bounds in shifted output coordinates
+    unsigned long long es, ps, ee;  // element start (header if TO_STREAM), payload start, end
+    auto bounds = [&](int el) {
+      if (TO_STREAM) {
+        es = A + s_off[el] + 4ull * el; ps = es + 4; ee = A + s_off[el + 1] + 4ull * (el + 1);
+      } else {
+        es = A + s_off[el]; ps = es; ee = A + s_off[el + 1];
+      }
+    };
+    bounds(e);
+    uint32_t w[4];
+#pragma unroll
+    for (int wi = 0; wi < 4; wi++) {
+      const unsigned long long wa = cb + 4 * wi;
+      w[wi] = 0;
+      if (wa >= b || wa + 4 <= a) continue;
+      while (ee <= wa && e + 1 < nE) { e++; bounds(e); }
+      // source offset of output byte p inside element el: TO_STREAM: blob[p - mis - 4*(E+1)],
+      // else stream[p - mis + 4*(E+1)], E = e0 + el
+      if (WORD_OK && wa >= ps && wa + 4 <= ee && wa >= a && wa + 4 <= b) {
+        const unsigned long long E1 = 4ull * (e0 + e + 1);
+        w[wi] = ldg_u32(src + (TO_STREAM ? wa - mis - E1 : wa - mis + E1));
+      } else {
+        uint32_t v = 0;
+#pragma unroll
+        for (int bi = 0; bi < 4; bi++) {
+          const unsigned long long p = wa + bi;
+          if (p < a || p >= b) continue;
+          while (ee <= p && e + 1 < nE) { e++; bounds(e); }
+          uint32_t byte;
+          if (TO_STREAM && p < ps) {
+            const unsigned long long len = s_off[e + 1] - s_off[e];
+            byte = (uint32_t)(len >> (8 * (p - es))) & 0xffu;
+          } else {
+            const unsigned long long E1 = 4ull * (e0 + e + 1);
+            byte = src[TO_STREAM ? p - mis - E1 : p - mis + E1];
+          }
+          v |= byte << (8 * bi);
+        }
+        w[wi] = v;
+      }
+    }
+    if (a == cb && b == cb + 16) {
+      st_v4(vd + cb, w[0], w[1], w[2], w[3]);
+    } else {
+      for (unsigned long long p = a; p < b; p++) vd[p] = (uint8_t)(w[(p - cb) >> 2] >> (8 * (p & 3)));
+    }
+  }
+}
+
+// LEN_SIZE: 4 or 8 bytes per length; FIXED: lengths come from fixed-width rows (trailing NULs
+// stripped) and the payload of element i starts at i * width instead of being packed.
+template <int LEN_SIZE, bool FIXED, bool WORD_OK>
+__global__ void __launch_bounds__(kSerThreads)
+k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ lengths,
+                  unsigned long long n, uint32_t width, uint8_t* __restrict__ dst,
+                  unsigned long long dst_capacity, unsigned long long* __restrict__ ws,
+                  unsigned long long* __restrict__ total_out) {
+  __shared__ unsigned long long s_off[kSerTile + 1];
+  __shared__ unsigned long long s_warp[kSerThreads / 32];
+  __shared__ unsigned long long s_prefix;
+  __shared__ unsigned int s_tile;
+  unsigned long long* status = ws + WS_HEADER_WORDS;
+  if (threadIdx.x == 0) s_tile = atomicAdd(reinterpret_cast<unsigned int*>(&ws[WS_TICKET]), 1u);
+  __syncthreads();
+  const unsigned int tile = s_tile;
+  const unsigned long long e0 = (unsigned long long)tile * kSerTile;
+  const int nE = (int)min((unsigned long long)kSerTile, n - e0);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  unsigned long long len[kSerItems];
+  unsigned long long tsum = 0;
+#pragma unroll
+  for (int i = 0; i < kSerItems; i++) {
+    const int el = threadIdx.x * kSerItems + i;
+    unsigned long long l = 0;
+    if (el < nE) {
+      if (FIXED) {
+        const uint8_t* row = payload + (e0 + el) * (unsigned long long)width;
+        uint32_t k = width;
+        while (k > 0 && row[k - 1] == 0) k--;  // numpy S<k>.item() strips trailing NULs
+        l = k;
+      } else if (LEN_SIZE == 4) {
+        l = reinterpret_cast<const uint32_t*>(lengths)[e0 + el];
+      } else {
+        l = reinterpret_cast<const unsigned long long*>(lengths)[e0 + el];
+      }
+    }
+    len[i] = l;
+    tsum += l;
+  }
+  // warp-shuffle inclusive scan of the per-thread sums, then across warps
+  unsigned long long incl = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  unsigned long long wbase = 0, tile_total = 0;
+#pragma unroll
+  for (int wdx = 0; wdx < kSerThreads / 32; wdx++) {
+    if (wdx < warp) wbase += s_warp[wdx];
+    tile_total += s_warp[wdx];
+  }
+  unsigned long long run = wbase + incl - tsum;
+#pragma unroll
+  for (int i = 0; i < kSerItems; i++) {
+    s_off[threadIdx.x * kSerItems + i] = run;
+    run += len[i];
+  }
+  if (threadIdx.x == kSerThreads - 1) s_off[kSerTile] = run;
+  if (warp == 0) {
+    const unsigned long long ex = lookback_exclusive(status, tile, tile_total, ws);
+    if (lane == 0) s_prefix = ex;
+  }
+  __syncthreads();
+  const unsigned long long blob0 = s_prefix;
+  if (e0 + nE == n && threadIdx.x == 0) {
+    const unsigned long long total = blob0 + s_off[nE] + 4ull * n;
+    ws[WS_TOTAL] = total;
+    if (total_out) *total_out = total;
+    if (total > dst_capacity) atomicMax(&ws[WS_ERROR], (unsigned long long)ERR_CAPACITY);
+  }
+  if (FIXED) {
+    // rows are not packed: element e's payload lives at (e0+e)*width, i.e. the "blob" coordinate
+    // of its first byte is not blob0 + s_off[e]. Byte path with explicit per-element source.
+    const unsigned long long o0 = blob0 + 4 * e0;
+    const unsigned long long o1 = min(blob0 + s_off[nE] + 4ull * (e0 + nE), dst_capacity);
+    for (unsigned long long p = o0 + threadIdx.x; p < o1; p += kSerThreads) {
+      const unsigned long long rel = p - o0;
+      int lo = 0, hi = nE;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (s_off[mid] + 4ull * mid <= rel) lo = mid; else hi = mid;
+      }
+      const unsigned long long es = s_off[lo] + 4ull * lo;
+      const unsigned long long l = s_off[lo + 1] - s_off[lo];
+      dst[p] = rel < es + 4 ? (uint8_t)(l >> (8 * (rel - es)))
+                            : payload[(e0 + lo) * (unsigned long long)width + (rel - es - 4)];
+    }
+  } else {
+    move_tile<true, WORD_OK>(s_off, nE, blob0, e0, payload, dst, dst_capacity);
+  }
+}
+
+// =================================================================================================
+// deserialise
+// =================================================================================================
+constexpr int kDesChunk = 8192;    // bytes of stream per chunk
+constexpr int kDesWindow = 512;    // look-behind window for the entry guess
+constexpr int kDesThreads = 128;
+constexpr int kDesListCap = 512;   // header positions recorded per chunk (uint16, chunk-relative)
+constexpr unsigned long long kNoGuess = ~0ull;
+
+// header words of the deserialise workspace
+enum : int {
+  DW_STATUS = 0,        // 0 ok, 1 needs sweep, 2 truncated
+  DW_NELEM = 1,         // elements decoded
+  DW_KEND = 2,          // last chunk that holds decoded elements (+1)
+  DW_FIRST_MISMATCH = 3,
+  DW_PAYLOAD = 4,       // payload bytes of the decoded elements
+  DW_SWEPT = 5,         // sticky: sweep ran
+  DW_HEADER_WORDS = 8
+};
+
+struct DesArrays {
+  unsigned long long* g;     // entry header position of chunk k (absolute stream offset)
+  unsigned long long* x;     // exit: first header position >= end of chunk k
+  unsigned long long* base;  // elements before chunk k
+  unsigned int* cnt;         // elements whose header lies in chunk k
+  unsigned int* err;         // 1: chain of chunk k hit a truncated header/payload after cnt elements
+  unsigned short* list;      // [K][kDesListCap] chunk-relative header positions
+};
+
+__device__ __forceinline__ uint32_t lds_u32_unaligned(const uint32_t* s, uint32_t byte_off) {
+  const uint32_t lo = s[byte_off >> 2], hi = s[(byte_off >> 2) + 1];
+  return __funnelshift_r(lo, hi, (byte_off & 3) * 8);
+}
+
+// Per chunk: stage [chunk start - window, chunk end + 4) in shared memory, vote for the entry
+// header, chase the chunk's chain.
+__global__ void __launch_bounds__(kDesThreads)
+k_des_speculate(const uint8_t* __restrict__ stream, unsigned long long S, unsigned long long K,
+                DesArrays A) {
+  constexpr int kStage = kDesWindow + kDesChunk + 16;
+  __shared__ __align__(16) uint32_t s_buf[kStage / 4 + 2];
+  __shared__ unsigned int s_votes[kDesWindow];
+  __shared__ unsigned int s_best;
+  const unsigned long long k = blockIdx.x;
+  const unsigned long long c0 = k * kDesChunk;                       // chunk start
+  const unsigned long long c1 = min(c0 + kDesChunk, S);              // chunk end
+  const unsigned long long lo = c0 >= kDesWindow ? c0 - kDesWindow : 0;
+  const unsigned long long hi = min(c1 + 16, S);
+  // stage (stream base + lo is 16-byte aligned when the stream base is: lo is a multiple of 512)
+  const bool aligned = (reinterpret_cast<uintptr_t>(stream) & 15) == 0;
+  const int nbytes = (int)(hi - lo);
+  if (aligned) {
+    const uint4* src = reinterpret_cast<const uint4*>(stream + lo);
+    uint4* d4 = reinterpret_cast<uint4*>(s_buf);
+    const int nvec = nbytes >> 4;
+    for (int i = threadIdx.x; i < nvec; i += kDesThreads) d4[i] = __ldg(src + i);
+    uint8_t* d8 = reinterpret_cast<uint8_t*>(s_buf);
+    for (int i = (nvec << 4) + threadIdx.x; i < nbytes; i += kDesThreads) d8[i] = stream[lo + i];
+  } else {
+    uint8_t* d8 = reinterpret_cast<uint8_t*>(s_buf);
+    for (int i = threadIdx.x; i < nbytes; i += kDesThreads) d8[i] = stream[lo + i];
+  }
+  for (int i = threadIdx.x; i < kDesWindow; i += kDesThreads) s_votes[i] = 0;
+  if (threadIdx.x == 0) s_best = 0;
+  __syncthreads();
+
+  unsigned long long g = 0;
+  if (k > 0) {
+    // every byte of the look-behind window is a candidate header; chase each to the chunk start
+    for (unsigned long long p0 = lo + threadIdx.x; p0 < c0; p0 += kDesThreads) {
+      unsigned long long pos = p0;
+      bool ok = true;
+      while (pos < c0) {
+        if (pos + 4 > S) { ok = false; break; }
+        const unsigned long long nx = pos + 4 + lds_u32_unaligned(s_buf, (uint32_t)(pos - lo));
+        if (nx > S) { ok = false; break; }
+        pos = nx;
+      }
+      if (ok && pos - c0 < kDesWindow) atomicAdd(&s_votes[pos - c0], 1u);
+    }
+    __syncthreads();
+    // plurality vote, ties to the smallest offset
+    unsigned int best = 0;
+    for (int i = threadIdx.x; i < kDesWindow; i += kDesThreads) {
+      const unsigned int v = s_votes[i];
+      if (v) best = max(best, (v << 16) | (unsigned int)(kDesWindow - 1 - i));
+    }
+    atomicMax(&s_best, best);
+    __syncthreads();
+    g = s_best ? c0 + (kDesWindow - 1 - (s_best & 0xffffu)) : kNoGuess;
+  }
+  if (threadIdx.x == 0) {
+    unsigned long long pos = g;
+    unsigned int n = 0, err = 0;
+    unsigned short* list = A.list + k * kDesListCap;
+    if (g != kNoGuess) {
+      while (pos < c1) {
+        if (pos + 4 > S) { err = 1; break; }
+        const unsigned long long nx = pos + 4 + lds_u32_unaligned(s_buf, (uint32_t)(pos - lo));
+        if (nx > S) { err = 1; break; }
+        if (n < kDesListCap) list[n] = (unsigned short)(pos - c0);
+        n++;
+        pos = nx;
+      }
+    }
+    A.g[k] = g; A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
+  }
+}
+
+// One chase step straight from global memory (sweep / overflow paths).
+__device__ __forceinline__ bool chase_global(const uint8_t* __restrict__ stream, unsigned long long S,
+                                             unsigned long long pos, unsigned long long* next) {
+  if (pos + 4 > S) return false;
+  const uint32_t l = (uint32_t)stream[pos] | ((uint32_t)stream[pos + 1] << 8) |
+                     ((uint32_t)stream[pos + 2] << 16) | ((uint32_t)stream[pos + 3] << 24);
+  const unsigned long long nx = pos + 4 + l;
+  if (nx > S) return false;
+  *next = nx;
+  return true;
+}
+
+// Single CTA: verify entry[k] == exit[k-1], scan counts, decide the outcome.
+__global__ void __launch_bounds__(1024)
+k_des_resolve(unsigned long long S, unsigned long long K, long long max_elements, DesArrays A,
+              unsigned long long* hdr) {
+  __shared__ unsigned long long s_part[1024];
+  __shared__ unsigned long long s_first, s_ferr;
+  const int t = threadIdx.x;
+  const unsigned long long per = (K + 1023) / 1024;
+  const unsigned long long k0 = min((unsigned long long)t * per, K), k1 = min(k0 + per, K);
+  if (t == 0) { s_first = K; s_ferr = K; }
+  __syncthreads();
+  // first chunk whose entry does not continue its predecessor's chain
+  unsigned long long first = K;
+  for (unsigned long long k = k0; k < k1; k++) {
+    const unsigned long long expect = k == 0 ? 0 : A.x[k - 1];
+    if (A.g[k] != expect) { first = k; break; }
+  }
+  if (first < K) atomicMin(&s_first, first);
+  __syncthreads();
+  first = s_first;
+  // exclusive scan of counts over the verified prefix [0, first); first truncated chunk in it
+  unsigned long long sum = 0, ferr = K;
+  for (unsigned long long k = k0; k < k1 && k < first; k++) {
+    sum += A.cnt[k];
+    if (ferr == K && A.err[k]) ferr = k;
+  }
+  if (ferr < K) atomicMin(&s_ferr, ferr);
+  s_part[t] = sum;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {
+    const unsigned long long v = t >= o ? s_part[t - o] : 0;
+    __syncthreads();
+    s_part[t] += v;
+    __syncthreads();
+  }
+  unsigned long long run = s_part[t] - sum;
+  for (unsigned long long k = k0; k < k1; k++) {
+    A.base[k] = run;
+    run += (k < first) ? A.cnt[k] : 0;
+  }
+  __syncthreads();
+  if (t == 0) {
+    const unsigned long long total = s_part[1023];  // elements in the verified prefix
+    ferr = s_ferr;
+    unsigned long long status, nelem, kend;
+    const bool limited = max_elements >= 0;
+    const unsigned long long M = limited ? (unsigned long long)max_elements : ~0ull;
+    // elements that decode before anything goes wrong inside the verified prefix
+    const unsigned long long good = ferr < K ? A.base[ferr] + A.cnt[ferr] : total;
+    if (limited && good >= M) {
+      unsigned long long lo = 0, hi = first;  // smallest kk with base[kk] + cnt[kk] >= M
+      while (lo < hi) {
+        const unsigned long long mid = (lo + hi) >> 1;
+        if (A.base[mid] + A.cnt[mid] >= M) hi = mid; else lo = mid + 1;
+      }
+      status = 0; nelem = M; kend = M == 0 ? 0 : lo + 1;
+    } else if (ferr < K) {
+      status = 2; nelem = good; kend = ferr + 1;  // the true chain runs off the buffer
+    } else if (first < K) {
+      status = 1; nelem = total; kend = first;    // a guessed entry was wrong: sweep
+    } else {
+      status = 0; nelem = total; kend = K;
+      const unsigned long long end = K ? A.x[K - 1] : 0;
+      if (end != S) status = 2;
+      if (limited) status = 2;  // fewer than M elements before the end: the reference unpacks past it
+    }
+    hdr[DW_STATUS] = status; hdr[DW_NELEM] = nelem; hdr[DW_KEND] = kend;
+    hdr[DW_FIRST_MISMATCH] = first;
+  }
+}
+
+// Sequential repair from the first mismatching chunk: re-chase chunks whose guessed entry was
+// wrong (or missing), pass through chunks that a long element skips. Exact by construction.
+__global__ void k_des_sweep(const uint8_t* __restrict__ stream, unsigned long long S,
+                            unsigned long long K, long long max_elements, DesArrays A,
+                            unsigned long long* hdr) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  unsigned long long k = hdr[DW_FIRST_MISMATCH];
+  unsigned long long count = k < K ? A.base[k] : 0;
+  unsigned long long e = k == 0 ? 0 : A.x[k - 1];
+  const bool limited = max_elements >= 0;
+  const unsigned long long M = limited ? (unsigned long long)max_elements : ~0ull;
+  bool trunc = false, stop = false;
+  hdr[DW_SWEPT] = 1;
+  for (; k < K; k++) {
+    const unsigned long long c0 = k * kDesChunk, c1 = min(c0 + kDesChunk, S);
+    if (stop || e >= c1) {  // nothing of the true chain starts in this chunk
+      A.g[k] = e; A.x[k] = e; A.cnt[k] = 0; A.err[k] = 0;
+      continue;
+    }
+    if (A.g[k] == e) {  // the guess was right after all
+      count += A.cnt[k];
+      if (A.err[k] && !(limited && count >= M)) { trunc = true; stop = true; }
+      e = A.x[k];
+      if (limited && count >= M) stop = true;
+      continue;
+    }
+    unsigned long long pos = e;
+    unsigned int n = 0, err = 0;
+    unsigned short* list = A.list + k * kDesListCap;
+    while (pos < c1) {
+      unsigned long long nx;
+      if (!chase_global(stream, S, pos, &nx)) { err = 1; break; }
+      if (n < kDesListCap) list[n] = (unsigned short)(pos - c0);
+      n++;
+      pos = nx;
+      if (limited && count + n >= M) break;
+    }
+    A.g[k] = e; A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
+    count += n;
+    e = pos;
+    if (limited && count >= M) { stop = true; A.err[k] = 0; }
+    else if (err) { trunc = true; stop = true; }
+  }
+  (void)trunc;  // the resolve pass that follows re-derives the outcome from the repaired arrays
+}
+
+// Element blob offsets: offsets[j] = header_pos(j) - 4*j for the elements whose header lies in
+// chunk k; the chunk holding the last decoded element also writes offsets[N].
+__global__ void __launch_bounds__(64)
+k_des_offsets(const uint8_t* __restrict__ stream, unsigned long long S, DesArrays A,
+              const unsigned long long* __restrict__ hdr, long long* __restrict__ offsets) {
+  const unsigned long long k = blockIdx.x;
+  const unsigned long long N = hdr[DW_NELEM];
+  if (hdr[DW_STATUS] != 0 || k >= hdr[DW_KEND]) return;
+  const unsigned long long base = A.base[k];
+  if (base >= N) return;
+  const unsigned long long c0 = k * kDesChunk;
+  const unsigned int n = (unsigned int)min((unsigned long long)A.cnt[k], N - base);
+  if (n == 0) return;
+  const bool last = base + n == N;
+  if (A.cnt[k] <= kDesListCap) {
+    const unsigned short* list = A.list + k * kDesListCap;
+    for (unsigned int i = threadIdx.x; i < n; i += blockDim.x)
+      offsets[base + i] = (long long)(c0 + list[i]) - 4ll * (long long)(base + i);
+    if (last && threadIdx.x == 0) {
+      unsigned long long nx = 0;
+      chase_global(stream, S, c0 + list[n - 1], &nx);
+      offsets[N] = (long long)nx - 4ll * (long long)N;
+    }
+  } else if (threadIdx.x == 0) {  // very short elements: re-chase this chunk
+    unsigned long long pos = A.g[k];
+    for (unsigned int i = 0; i < n; i++) {
+      offsets[base + i] = (long long)pos - 4ll * (long long)(base + i);
+      unsigned long long nx = pos;
+      chase_global(stream, S, pos, &nx);
+      pos = nx;
+    }
+    if (last) offsets[N] = (long long)pos - 4ll * (long long)N;
+  }
+}
+
+constexpr int kGatTile = 1024;
+constexpr int kGatThreads = 256;
+
+template <bool WORD_OK>
+__global__ void __launch_bounds__(kGatThreads)
+k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ offsets,
+             const unsigned long long* __restrict__ hdr, uint8_t* __restrict__ blob,
+             unsigned long long blob_capacity) {
+  __shared__ unsigned long long s_off[kGatTile + 1];
+  const unsigned long long N = hdr[DW_NELEM];
+  if (hdr[DW_STATUS] != 0) return;
+  const unsigned long long e0 = (unsigned long long)blockIdx.x * kGatTile;
+  if (e0 >= N) return;
+  const int nE = (int)min((unsigned long long)kGatTile, N - e0);
+  const unsigned long long b0 = (unsigned long long)offsets[e0];
+  for (int i = threadIdx.x; i <= nE; i += kGatThreads)
+    s_off[i] = (unsigned long long)offsets[e0 + i] - b0;
+  __syncthreads();
+  move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity);
+}
+
+static uint64_t des_chunks(uint64_t stream_bytes) { return (stream_bytes + kDesChunk - 1) / kDesChunk; }
+
+}  // namespace tcb
+
+using namespace tcb;
+
+extern "C" {
+
+uint64_t TcbBytesSerializeWorkspace(uint64_t n_elements) {
+  const uint64_t tiles = (n_elements + kSerTile - 1) / kSerTile;
+  return (WS_HEADER_WORDS + tiles + 1) * 8;
+}
+
+uint64_t TcbBytesDeserializeWorkspace(uint64_t stream_bytes) {
+  const uint64_t K = des_chunks(stream_bytes) + 1;
+  // header + g, x, base (u64) + cnt, err (u32) + list (u16 * cap), each 256-byte aligned
+  return 256 + 3 * round_up(K * 8, 256) + 2 * round_up(K * 4, 256) +
+         round_up(K * kDesListCap * 2, 256);
+}
+
+static int serialize_common(int device_id, const void* payload_dev, const void* lengths_dev,
+                            int length_size, bool fixed, uint32_t width, uint64_t n, void* dst_dev,
+                            uint64_t dst_capacity, void* workspace_dev, uint64_t workspace_bytes,
+                            uint64_t* total_dev, uint64_t* total_host, void* stream) {
+  TCB_CHECK_ARG(fixed || length_size == 4 || length_size == 8, "TcbBytesSerialize: length_size must be 4 or 8");
+  TCB_DEVICE_GUARD(device_id);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (n == 0) {
+    if (total_dev) TCB_CUDA(cudaMemsetAsync(total_dev, 0, 8, s));
+    if (total_host) { TCB_CUDA(cudaStreamSynchronize(s)); *total_host = 0; }
+    return TCB_OK;
+  }
+  TCB_CHECK_ARG(payload_dev != nullptr || !fixed, "TcbBytesSerialize: payload is NULL");
+  TCB_CHECK_ARG(fixed || lengths_dev != nullptr, "TcbBytesSerialize: lengths is NULL");
+  TCB_CHECK_ARG(dst_dev != nullptr && workspace_dev != nullptr, "TcbBytesSerialize: NULL dst/workspace");
+  const uint64_t need = TcbBytesSerializeWorkspace(n);
+  if (workspace_bytes < need)
+    return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesSerialize: workspace needs %llu bytes, got %llu",
+                     (unsigned long long)need, (unsigned long long)workspace_bytes);
+  TCB_CHECK_ARG(reinterpret_cast<uintptr_t>(workspace_dev) % 8 == 0, "TcbBytesSerialize: workspace not 8-byte aligned");
+  TCB_CHECK_ARG(fixed || reinterpret_cast<uintptr_t>(lengths_dev) % length_size == 0,
+                "TcbBytesSerialize: lengths not aligned");
+  const uint64_t tiles = (n + kSerTile - 1) / kSerTile;
+  TCB_CHECK_ARG(tiles < (1ull << 31), "TcbBytesSerialize: too many elements");
+  unsigned long long* ws = static_cast<unsigned long long*>(workspace_dev);
+  TCB_CUDA(cudaMemsetAsync(ws, 0, need, s));
+  const uint8_t* pay = static_cast<const uint8_t*>(payload_dev);
+  uint8_t* dst = static_cast<uint8_t*>(dst_dev);
+  const bool word_ok = ((reinterpret_cast<uintptr_t>(pay) ^ reinterpret_cast<uintptr_t>(dst)) & 3) == 0;
+  unsigned long long* tot = reinterpret_cast<unsigned long long*>(total_dev);
+#define TCB_SER(LS, FX, WO)                                                                     \
+  k_bytes_serialize<LS, FX, WO><<<(unsigned)tiles, kSerThreads, 0, s>>>(pay, lengths_dev, n, width, dst, \
+                                                                        dst_capacity, ws, tot)
+  if (fixed) TCB_SER(4, true, false);
+  else if (length_size == 4) { if (word_ok) TCB_SER(4, false, true); else TCB_SER(4, false, false); }
+  else { if (word_ok) TCB_SER(8, false, true); else TCB_SER(8, false, false); }
+#undef TCB_SER
+  count_launch();
+  TCB_CUDA(cudaGetLastError());
+  if (total_host) {
+    unsigned long long h[WS_HEADER_WORDS];
+    TCB_CUDA(cudaMemcpyAsync(h, ws, sizeof(h), cudaMemcpyDeviceToHost, s));
+    TCB_CUDA(cudaStreamSynchronize(s));
+    *total_host = h[WS_TOTAL];
+    if (h[WS_ERROR] == ERR_SPIN) return set_error(TCB_ERR_INTERNAL, "TcbBytesSerialize: look-back scan timed out");
+    if (h[WS_ERROR] == ERR_CAPACITY)
+      return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesSerialize: serialized size %llu exceeds capacity %llu",
+                       (unsigned long long)h[WS_TOTAL], (unsigned long long)dst_capacity);
+  }
+  return TCB_OK;
+}
+
+int TcbBytesSerialize(int device_id, const void* payload_dev, const void* lengths_dev,
+                      int length_size, uint64_t n_elements, void* dst_dev, uint64_t dst_capacity,
+                      void* workspace_dev, uint64_t workspace_bytes, uint64_t* total_dev,
+                      uint64_t* total_host, void* stream) {
+  return serialize_common(device_id, payload_dev, lengths_dev, length_size, false, 0, n_elements, dst_dev,
+                          dst_capacity, workspace_dev, workspace_bytes, total_dev, total_host, stream);
+}
+
+int TcbBytesSerializeFixedWidth(int device_id, const void* rows_dev, uint32_t width,
+                                uint64_t n_elements, void* dst_dev, uint64_t dst_capacity,
+                                void* workspace_dev, uint64_t workspace_bytes,
+                                uint64_t* total_dev, uint64_t* total_host, void* stream) {
+  TCB_CHECK_ARG(width > 0 || n_elements == 0, "TcbBytesSerializeFixedWidth: width must be positive");
+  return serialize_common(device_id, rows_dev, nullptr, 4, true, width, n_elements, dst_dev, dst_capacity,
+                          workspace_dev, workspace_bytes, total_dev, total_host, stream);
+}
+
+int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_bytes,
+                        int64_t max_elements, int64_t* offsets_dev, uint64_t offsets_capacity,
+                        void* payload_dev, uint64_t payload_capacity, void* workspace_dev,
+                        uint64_t workspace_bytes, uint64_t* n_elements_host,
+                        uint64_t* payload_bytes_host, void* stream) {
+  TCB_CHECK_ARG(n_elements_host != nullptr, "TcbBytesDeserialize: n_elements_host is NULL");
+  *n_elements_host = 0;
+  if (payload_bytes_host) *payload_bytes_host = 0;
+  TCB_DEVICE_GUARD(device_id);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  TCB_CHECK_ARG(offsets_dev != nullptr, "TcbBytesDeserialize: offsets is NULL");
+  if (max_elements == 0 || (stream_bytes == 0 && max_elements < 0)) {
+    TCB_CUDA(cudaMemsetAsync(offsets_dev, 0, 8, s));
+    TCB_CUDA(cudaStreamSynchronize(s));
+    return TCB_OK;
+  }
+  if (stream_bytes == 0)
+    return set_error(TCB_ERR_TRUNCATED, "TcbBytesDeserialize: empty buffer but %lld elements requested",
+                     (long long)max_elements);
+  TCB_CHECK_ARG(stream_dev != nullptr && workspace_dev != nullptr, "TcbBytesDeserialize: NULL stream/workspace");
+  const uint64_t need = TcbBytesDeserializeWorkspace(stream_bytes);
+  if (workspace_bytes < need)
+    return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesDeserialize: workspace needs %llu bytes, got %llu",
+                     (unsigned long long)need, (unsigned long long)workspace_bytes);
+  TCB_CHECK_ARG(reinterpret_cast<uintptr_t>(workspace_dev) % 256 == 0, "TcbBytesDeserialize: workspace not 256-byte aligned");
+  const uint64_t K = des_chunks(stream_bytes);
+  TCB_CHECK_ARG(K < (1ull << 31), "TcbBytesDeserialize: stream too large");
+  uint8_t* w = static_cast<uint8_t*>(workspace_dev);
+  unsigned long long* hdr = reinterpret_cast<unsigned long long*>(w);
+  DesArrays A;
+  uint8_t* p = w + 256;
+  const uint64_t K1 = K + 1;
+  A.g = reinterpret_cast<unsigned long long*>(p); p += round_up(K1 * 8, 256);
+  A.x = reinterpret_cast<unsigned long long*>(p); p += round_up(K1 * 8, 256);
+  A.base = reinterpret_cast<unsigned long long*>(p); p += round_up(K1 * 8, 256);
+  A.cnt = reinterpret_cast<unsigned int*>(p); p += round_up(K1 * 4, 256);
+  A.err = reinterpret_cast<unsigned int*>(p); p += round_up(K1 * 4, 256);
+  A.list = reinterpret_cast<unsigned short*>(p);
+  const uint8_t* st = static_cast<const uint8_t*>(stream_dev);
+  TCB_CUDA(cudaMemsetAsync(hdr, 0, 256, s));
+  k_des_speculate<<<(unsigned)K, kDesThreads, 0, s>>>(st, stream_bytes, K, A);
+  k_des_resolve<<<1, 1024, 0, s>>>(stream_bytes, K, max_elements, A, hdr);
+  count_launch(2);
+  unsigned long long h[DW_HEADER_WORDS];
+  TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
+  TCB_CUDA(cudaStreamSynchronize(s));
+  if (h[DW_STATUS] == 1) {  // a guess was wrong: repair sequentially, then resolve again
+    k_des_sweep<<<1, 32, 0, s>>>(st, stream_bytes, K, max_elements, A, hdr);
+    k_des_resolve<<<1, 1024, 0, s>>>(stream_bytes, K, max_elements, A, hdr);
+    count_launch(2);
+    TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
+    TCB_CUDA(cudaStreamSynchronize(s));
+  }
+  if (h[DW_STATUS] == 2)
+    return set_error(TCB_ERR_TRUNCATED, "TcbBytesDeserialize: buffer ends inside an element after %llu elements",
+                     (unsigned long long)h[DW_NELEM]);
+  if (h[DW_STATUS] != 0)
+    return set_error(TCB_ERR_INTERNAL, "TcbBytesDeserialize: chunk chain did not resolve (status %llu)",
+                     (unsigned long long)h[DW_STATUS]);
+  const uint64_t N = h[DW_NELEM];
+  if (N > offsets_capacity)
+    return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesDeserialize: %llu elements exceed offsets capacity %llu",
+                     (unsigned long long)N, (unsigned long long)offsets_capacity);
+  *n_elements_host = N;
+  if (N == 0) {
+    TCB_CUDA(cudaMemsetAsync(offsets_dev, 0, 8, s));
+    TCB_CUDA(cudaStreamSynchronize(s));
+    return TCB_OK;
+  }
+  k_des_offsets<<<(unsigned)h[DW_KEND], 64, 0, s>>>(st, stream_bytes, A, hdr, reinterpret_cast<long long*>(offsets_dev));
+  count_launch();
+  long long total = 0;
+  TCB_CUDA(cudaMemcpyAsync(&total, offsets_dev + N, 8, cudaMemcpyDeviceToHost, s));
+  TCB_CUDA(cudaStreamSynchronize(s));
+  if (payload_bytes_host) *payload_bytes_host = (uint64_t)total;
+  if (total > 0) {
+    TCB_CHECK_ARG(payload_dev != nullptr, "TcbBytesDeserialize: payload is NULL");
+    if ((uint64_t)total > payload_capacity)
+      return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesDeserialize: payload of %lld bytes exceeds capacity %llu",
+                       total, (unsigned long long)payload_capacity);
+    uint8_t* blob = static_cast<uint8_t*>(payload_dev);
+    const unsigned tiles = (unsigned)((N + kGatTile - 1) / kGatTile);
+    const bool word_ok = ((reinterpret_cast<uintptr_t>(st) ^ reinterpret_cast<uintptr_t>(blob)) & 3) == 0;
+    if (word_ok)
+      k_des_gather<true><<<tiles, kGatThreads, 0, s>>>(st, reinterpret_cast<long long*>(offsets_dev), hdr, blob, payload_capacity);
+    else
+      k_des_gather<false><<<tiles, kGatThreads, 0, s>>>(st, reinterpret_cast<long long*>(offsets_dev), hdr, blob, payload_capacity);
+    count_launch();
+  }
+  TCB_CUDA(cudaGetLastError());
+  TCB_CUDA(cudaStreamSynchronize(s));
+  return TCB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,187 @@
+"""Drop-in for ``image_client.py``'s ``preprocess`` on a B200, plus the batched form that
+writes straight into a registered CUDA shared-memory region.
+
+``preprocess(img, format, dtype, c, h, w, scaling, protocol)`` keeps the signature and the
+results of /root/reference/src/python/examples/image_client.py:154-193. What runs where:
+
+* Pillow's ``convert`` + ``resize(BILINEAR)`` (22-bit fixed point, uint8 between the two passes),
+  the dtype cast, INCEPTION / VGG / NONE scaling and the NHWC/NCHW ordering: CUDA kernels in
+  libtcb200.so (``TcbPreprocessPlan*`` in include/tcb200.h). No CPU fallback.
+* The 256-entry value table per channel is built here by evaluating the reference's own numpy
+  expressions on every uint8 value, which makes cast + scaling bit-exact for every dtype.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from ._device import current_device, device_buffer, stream_ptr, to_device_u8, to_host
+from .utils import triton_to_np_dtype
+
+FORMAT_NONE, FORMAT_NHWC, FORMAT_NCHW = 0, 1, 2  # model_config.proto ModelInput.Format
+
+
+def scaling_table(dtype, c, scaling):
+    """lut[c, 256]: image_client.py:171-182 applied to arange(256) with numpy itself."""
+    npdtype = triton_to_np_dtype(dtype)
+    resized = np.repeat(np.arange(256, dtype=np.uint8)[:, None, None], c, axis=2)  # [256, 1, c]
+    typed = resized.astype(npdtype)
+    if scaling == "INCEPTION":
+        scaled = (typed / 127.5) - 1
+    elif scaling == "VGG":
+        if c == 1:
+            scaled = typed - np.asarray((128,), dtype=npdtype)
+        else:
+            scaled = typed - np.asarray((123, 117, 104), dtype=npdtype)
+    else:
+        scaled = typed
+    return np.ascontiguousarray(scaled[:, 0, :].T)
+
+
+class PreprocessPlan:
+    """Geometry-bound plan for a batch of images: owns Pillow's coefficient tables, descriptors
+    and scratch on the device (``TcbPreprocessPlanCreate``). ``sizes`` is a list of
+    (width, height, src_channels) or (width, height, src_channels, pitch)."""
+
+    def __init__(self, sizes, format, dtype, c, h, w, scaling, device=None, path=0):
+        self.device = current_device() if device is None else int(device)
+        self.n = len(sizes)
+        self.c, self.h, self.w = int(c), int(h), int(w)
+        self.layout = _lib.LAYOUT_NCHW if format == FORMAT_NCHW else _lib.LAYOUT_NHWC
+        self.lut = scaling_table(dtype, self.c, scaling)
+        if self.lut.dtype.kind not in "biuf":
+            raise TypeError("preprocess: unsupported result dtype %s" % self.lut.dtype)
+        self.out_dtype = self.lut.dtype
+        self.elem = self.lut.dtype.itemsize
+        self.images = (_lib.TcbImage * self.n)()
+        for i, s in enumerate(sizes):
+            wd, ht, ch = int(s[0]), int(s[1]), int(s[2])
+            pitch = int(s[3]) if len(s) > 3 else wd * ch
+            self.images[i] = _lib.TcbImage(0, wd, ht, pitch, ch)
+        self.sizes = [(im.width, im.height, im.src_channels, im.pitch) for im in self.images]
+        self._plan = ctypes.c_void_p()
+        self._path = path
+        self._created = False
+        self.out_bytes_per_image = self.c * self.h * self.w * self.elem
+
+    @property
+    def out_shape(self):
+        if self.layout == _lib.LAYOUT_NCHW:
+            return (self.n, self.c, self.h, self.w)
+        return (self.n, self.h, self.w, self.c)
+
+    def _ensure(self, ptrs):
+        for i, p in enumerate(ptrs):
+            self.images[i].src_dev = int(p)
+        if not self._created:
+            # created lazily with real pointers: the fused kernel's eligibility depends on alignment
+            _lib.check(_lib.lib.TcbPreprocessPlanCreate(
+                self.device, self.images, self.n, self.c, self.h, self.w, self.layout,
+                self.lut.ctypes.data, self.elem, self._path, ctypes.byref(self._plan)))
+            self._created = True
+            return None
+        return self.images
+
+    def info(self):
+        scratch, per, fused = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_int()
+        _lib.check(_lib.lib.TcbPreprocessPlanInfo(self._plan, ctypes.byref(scratch), ctypes.byref(per),
+                                                  ctypes.byref(fused)))
+        return {"scratch_bytes": scratch.value, "out_bytes_per_image": per.value,
+                "fused_images": fused.value}
+
+    def run(self, src_ptrs, dst_ptr, dst_capacity, stream=None):
+        """Enqueue the batch: src_ptrs[i] is the device address of image i's first pixel."""
+        imgs = self._ensure(src_ptrs)
+        s = stream_ptr(self.device) if stream is None else stream
+        _lib.check(_lib.lib.TcbPreprocessPlanRun(self._plan, imgs, dst_ptr, int(dst_capacity), s))
+
+    def close(self):
+        if self._created:
+            self._created = False
+            _lib.lib.TcbPreprocessPlanDestroy(self._plan)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def preprocess_batch(images, format, dtype, c, h, w, scaling, out=None, out_offset=0, plan=None,
+                     device=None, sync=True):
+    """Preprocess a batch of device-resident uint8 images into ``out``.
+
+    images : list of torch uint8 CUDA tensors shaped [H, W] / [H, W, C] (C in 1, 3, 4), possibly
+             of different sizes, or one tensor [N, H, W, C]
+    out    : ``CudaSharedMemoryRegion`` or torch CUDA tensor (bytes written from ``out_offset``), or
+             None to get a new torch tensor of the result dtype
+    Returns (out, plan); pass ``plan`` back in to reuse it for the same geometry."""
+    import torch
+
+    if isinstance(images, torch.Tensor) and images.dim() == 4:
+        images = list(images.unbind(0))
+    dev = images[0].device.index if device is None else device
+    sizes, ptrs = [], []
+    for t in images:
+        if t.dtype != torch.uint8 or not t.is_cuda:
+            raise TypeError("images must be uint8 CUDA tensors")
+        ch = 1 if t.dim() == 2 else int(t.shape[2])
+        if t.stride(-1) != 1 or (t.dim() == 3 and t.stride(1) != ch):
+            raise ValueError("image rows must be densely packed (stride of x must equal channels)")
+        sizes.append((int(t.shape[1]), int(t.shape[0]), ch, int(t.stride(0))))
+        ptrs.append(t.data_ptr())
+    if plan is None or plan.sizes != [tuple(s) for s in sizes]:
+        plan = PreprocessPlan(sizes, format, dtype, c, h, w, scaling, device=dev)
+    if out is None:
+        tdt = {"float32": torch.float32, "float16": torch.float16, "float64": torch.float64,
+               "uint8": torch.uint8, "int8": torch.int8, "int16": torch.int16, "int32": torch.int32,
+               "int64": torch.int64}.get(str(plan.out_dtype))
+        if tdt is None:
+            out = torch.empty(plan.n * plan.out_bytes_per_image, dtype=torch.uint8, device="cuda:%d" % dev)
+        else:
+            out = torch.empty(plan.out_shape, dtype=tdt, device="cuda:%d" % dev)
+    from .utils import _dst_of
+
+    dst_ptr, cap = _dst_of(out, out_offset)
+    plan.run(ptrs, dst_ptr, cap)
+    if sync:
+        _lib.check(_lib.lib.TcbStreamSync(dev, stream_ptr(dev)))
+    return out, plan
+
+
+def _pil_to_array(img, c):
+    """uint8 array [H, W, Cin] of the PIL image. L / RGB / RGBA pixels are handed to the GPU as
+    they are (the kernels implement Pillow's conversions between them); any other mode (palette,
+    CMYK, 16-bit, ...) is first decoded by Pillow itself, which is file-format glue rather than
+    the resampling path."""
+    if img.mode not in ("L", "RGB", "RGBA"):
+        img = img.convert("L" if c == 1 else "RGB")
+    a = np.asarray(img)
+    if a.ndim == 2:
+        a = a[:, :, None]
+    return np.ascontiguousarray(a)
+
+
+_plan_cache = {}
+
+
+def preprocess(img, format, dtype, c, h, w, scaling, protocol=None):
+    """Pre-process one PIL image to the size, type and format requirements given (same contract
+    as the reference's ``preprocess``); returns a numpy array shaped (c, h, w) for FORMAT_NCHW,
+    else (h, w, c)."""
+    c, h, w = int(c), int(h), int(w)
+    src = _pil_to_array(img, c)
+    dev = current_device()
+    H, W, cin = src.shape
+    key = (dev, W, H, cin, format == FORMAT_NCHW, dtype, c, h, w, scaling)
+    plan = _plan_cache.get(key)
+    if plan is None:
+        if len(_plan_cache) > 64:
+            _plan_cache.clear()
+        plan = PreprocessPlan([(W, H, cin)], format, dtype, c, h, w, scaling, device=dev)
+        _plan_cache[key] = plan
+    d_src = to_device_u8(src, dev)
+    d_out = device_buffer(plan.out_bytes_per_image, dev)
+    plan.run([d_src.data_ptr()], d_out.data_ptr(), plan.out_bytes_per_image)
+    host = to_host(d_out.data_ptr(), plan.out_bytes_per_image, dev)  # synchronises
+    return host.view(plan.out_dtype).reshape(plan.out_shape[1:])
