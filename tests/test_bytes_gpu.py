@@ -148,11 +148,15 @@ def test_roundtrip_edge_lengths():
 def test_truncated_streams_raise_struct_error():
     from triton_client_b200 import utils as u
 
-    good = bc.serialize_elements(np.array([b"abc", b"de", b"f" * 9000, b""], dtype=np.object_))
-    for cut in (1, 2, 3, 5, 6, 8, 12, 13, 5000, len(good) - 4, len(good) - 1):
+    good = bc.serialize_elements(np.array([b"abc", b"de", b"f" * 9000, b"", b"zz"], dtype=np.object_))
+    for cut in (1, 2, 3, 5, 6, 8, 12, 14, 5000, len(good) - 5, len(good) - 3, len(good) - 1):
+        with pytest.raises(struct.error):
+            bc.deserialize_stream(good[:cut])      # the reference's behaviour (oracle restatement)
         with pytest.raises(struct.error):
             u.deserialize_bytes_tensor(good[:cut])
-    assert len(u.deserialize_bytes_tensor(good)) == 4
+    for cut in (7, 13, len(good) - 6, len(good) - 10):  # cuts on an element boundary are valid streams
+        assert list(u.deserialize_bytes_tensor(good[:cut])) == bc.deserialize_stream(good[:cut])
+    assert len(u.deserialize_bytes_tensor(good)) == 5
     assert u.deserialize_bytes_tensor(b"").shape == (0,)
     # a header that claims more than the buffer holds
     with pytest.raises(struct.error):
