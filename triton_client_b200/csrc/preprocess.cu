@@ -261,7 +261,8 @@ static void plan_free(Plan* p) {
   if (!p) return;
   DeviceGuard g(p->device);
   cudaFree(p->d_desc); cudaFree(p->d_pool); cudaFree(p->d_lut); cudaFree(p->d_scratch);
-  cudaFree(p->d_blk1); cudaFree(p->d_blk2); cudaFree(p->d_fused_work);
+  cudaFree(p->d_blk1); cudaFree(p->d_blk2);
+  fused_release(*p);
   delete p;
 }
 
@@ -341,7 +342,7 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
   };
 
   p->h_desc.resize(n_images);
-  std::vector<int32_t> blk1(n_images + 1, 0), blk2(n_images + 1, 0), fused_work;
+  std::vector<int32_t> blk1(n_images + 1, 0), blk2(n_images + 1, 0);
   uint64_t scratch = 0;
   size_t fused_smem = 0;
   for (int i = 0; i < n_images; i++) {
@@ -364,7 +365,6 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
     if (can_fuse) {
       d.fused = 1; d.band_rows = band;
       fused_smem = std::max(fused_smem, smem);
-      for (int y0 = 0; y0 < out_h; y0 += band) { fused_work.push_back(i); fused_work.push_back(y0); }
       p->n_fused_images++;
       blk1[i + 1] = blk1[i]; blk2[i + 1] = blk2[i];
       continue;
@@ -380,7 +380,7 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
   }
   p->blocks1 = blk1[n_images]; p->blocks2 = blk2[n_images];
   p->scratch_bytes = scratch; p->pool_words = pool.size();
-  p->n_fused_ctas = (int)(fused_work.size() / 2); p->fused_smem = fused_smem;
+  p->n_fused_ctas = p->n_fused_images; p->fused_smem = fused_smem;
   if (pool.empty()) pool.push_back(0);
 
   int rc = upload((void**)&p->d_desc, p->h_desc.data(), sizeof(ImgDesc) * n_images);
@@ -388,8 +388,7 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
   if (!rc) rc = upload((void**)&p->d_lut, lut, (size_t)c * 256 * elem_size);
   if (!rc) rc = upload((void**)&p->d_blk1, blk1.data(), blk1.size() * sizeof(int32_t));
   if (!rc) rc = upload((void**)&p->d_blk2, blk2.data(), blk2.size() * sizeof(int32_t));
-  if (!rc && !fused_work.empty())
-    rc = upload((void**)&p->d_fused_work, fused_work.data(), fused_work.size() * sizeof(int32_t));
+  if (!rc && p->n_fused_images > 0) rc = fused_prepare(*p);
   if (!rc && scratch > 0) {
     cudaError_t e = cudaMalloc((void**)&p->d_scratch, scratch);
     if (e != cudaSuccess)
@@ -448,9 +447,12 @@ int TcbPreprocessPlanRun(void* plan, const TcbImage* images_or_null, void* dst_d
       }
     }
     // pageable source: cudaMemcpyAsync returns once the host buffer has been staged
-    if (changed)
+    if (changed) {
       TCB_CUDA(cudaMemcpyAsync(p->d_desc, p->h_desc.data(), sizeof(ImgDesc) * p->n,
                                cudaMemcpyHostToDevice, s));
+      int rc = fused_update_sources(*p, s);
+      if (rc) return rc;
+    }
   }
   for (int i = 0; i < p->n; i++)
     TCB_CHECK_ARG(p->h_desc[i].src != nullptr, "TcbPreprocessPlanRun: image %d has no source pointer", i);

@@ -56,6 +56,9 @@ int compute_axis_coeffs(int in_size, int out_size, std::vector<int32_t>& bounds,
 
 // fused kernel (preprocess_fused.cu)
 bool fused_supported(const Plan& p, const ImgDesc& d, int* band_rows, size_t* smem_bytes);
+int fused_prepare(Plan& p);                                // after h_desc is final
+int fused_update_sources(const Plan& p, cudaStream_t s);   // after src/pitch changed
 int fused_launch(const Plan& p, void* dst, cudaStream_t stream);
+void fused_release(const Plan& p);
 
 }  // namespace tcb

@@ -1,13 +1,573 @@
-// Fused single-kernel preprocess path (placeholder until the kernel lands: nothing is eligible,
-// every image takes the two-pass kernels of preprocess.cu).
+// Fused single-kernel preprocess (sm_100a): PIL-exact BILINEAR resample (H pass -> uint8 -> V pass
+// -> uint8) + value table + NHWC/NCHW store, one launch per coefficient-width class.
+//
+// Replaces image_client.py:154-193 (/root/reference/src/python/examples/image_client.py) for the
+// common case "both axes resampled, horizontal pass first"; every other geometry takes the
+// two-pass kernels in preprocess.cu. Arithmetic is the one restated in oracle/ (Pillow
+// Resample.c): acc = 2^21 + sum(px * k), k 22-bit fixed point, clip8(acc >> 22).
+//
+// Per CTA = (image, band of output rows). Source rows stream through the CTA four at a time:
+//   1. TMA bulk copy (cp.async.bulk + mbarrier complete_tx) of 4 interleaved source rows into a
+//      2-3 stage shared-memory ring; issued by one thread, NST groups ahead.
+//   2. de-interleave to planar, 4-row-interleaved words P4[ch][word][row] (PRMT byte shuffles).
+//   3. horizontal pass with dp4a: thread = output column xx; its coefficients live in registers
+//      as three byte planes (k = k0 + k1<<8 + k2<<16) aligned to the 4-pixel word grid; one
+//      128-bit LDS brings the same 4 pixels of all 4 rows; 12 dp4a per load.
+//      The four uint8 results (rows 4g..4g+3) are packed into one word of a small ring tmp4[g].
+//   4. vertical pass, again dp4a (the 4 rows of a word are 4 vertical taps), as soon as the last
+//      row group an output row needs has arrived; then the 256-entry table and a vector store
+//      straight to the destination (the registered region).
+// HBM traffic is the source once (+ the band halo) and the output once.
+#include <algorithm>
+#include <array>
+#include <map>
+
 #include "preprocess.cuh"
 
 namespace tcb {
 
-bool fused_supported(const Plan&, const ImgDesc&, int*, size_t*) { return false; }
+constexpr int kFusedMaxThreads = 512;
+constexpr size_t kFusedMaxSmem = 200 * 1024;
+static const int kNwClasses[] = {2, 3, 4, 6, 8, 12, 16};
 
-int fused_launch(const Plan&, void*, cudaStream_t) {
-  return set_error(TCB_ERR_INTERNAL, "fused preprocess kernel not built");
+// ---- PTX helpers ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 1-D TMA: global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void st_global_v4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void st_global_v2(void* p, uint32_t a, uint32_t b) {
+  asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+
+// fused-kernel view of one image (lives in the plan's descriptor array next to ImgDesc)
+struct FusedDesc {
+  const uint8_t* src;
+  int32_t W, H, pitch, cin;
+  int32_t nw;        // horizontal coefficient words per output column (class)
+  int32_t nwv;       // vertical coefficient words per output row
+  int32_t hc_off;    // pool: packed H coefficients [out_w][nw][3]
+  int32_t hw0_off;   // pool: first source word of every output column [out_w]
+  int32_t vc_off;    // pool: packed V coefficients [out_h][nwv][3]
+  int32_t vg_off;    // pool: (first group, last group) of every output row [out_h][2]
+  int32_t vb_off;    // pool: Pillow bounds of the vertical axis [out_h][2]
+  int32_t band_rows;
+  int32_t wq;        // words per planar row incl. padding
+  int32_t stage_bytes;
+  int32_t nst;       // TMA stages
+  int32_t aligned4;  // rows start 4-byte aligned: PRMT de-interleave applies
+};
+
+__device__ __forceinline__ uint32_t fetch_conv(const uint8_t* row, int cin, int C, int x, int ch) {
+  if (C == 3) {
+    if (cin == 1) return row[x];
+    return row[x * cin + ch];
+  }
+  if (cin == 1) return row[x];
+  const uint8_t* q = row + x * cin;
+  return (q[0] * 19595u + q[1] * 38470u + q[2] * 7471u + 0x8000u) >> 16;
+}
+
+// NW: coefficient words per output column; C: output channels.
+template <int NW, int C>
+__global__ void __launch_bounds__(kFusedMaxThreads, 1)
+k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restrict__ work,
+                   const int32_t* __restrict__ pool, const uint8_t* __restrict__ lut,
+                   uint8_t* __restrict__ dst, int out_h, int out_w, int layout, int elem,
+                   int dst_aligned16) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int img = work[2 * blockIdx.x], yy0 = work[2 * blockIdx.x + 1];
+  const FusedDesc d = descs[img];
+  const int tid = threadIdx.x, nthreads = blockDim.x;
+  const int yy1 = min(yy0 + d.band_rows, out_h);
+  const int L = out_w * C;  // words per tmp4 slot / elements per output row
+  const int ng = d.nwv + 1;
+
+  // ---- shared memory carve-up -------------------------------------------------------------------
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                   // [nst]
+  uint8_t* s_lut = smem + 64;                                           // C*256*elem
+  uint8_t* raw = smem + 64 + ((C * 256 * elem + 127) & ~127);           // nst stages
+  uint4* P4 = reinterpret_cast<uint4*>(raw + (size_t)d.nst * d.stage_bytes);  // [C][wq]
+  uint32_t* tmp4 = reinterpret_cast<uint32_t*>(P4 + (size_t)C * d.wq);  // [ng][L]
+
+  // source row groups this band needs
+  const int32_t* vb = pool + d.vb_off;
+  const int ys = vb[2 * yy0], ye = vb[2 * (yy1 - 1)] + vb[2 * (yy1 - 1) + 1];  // rows [ys, ye)
+  const int g_first = ys >> 2, g_last = (ye - 1) >> 2;
+
+  auto issue = [&](int g) {  // thread 0: TMA for row group g into its stage
+    const int s = (g - g_first) % d.nst;
+    const int r1 = min(4 * g + 4, d.H);
+    const uintptr_t start = reinterpret_cast<uintptr_t>(d.src) + (size_t)(4 * g) * d.pitch;
+    const uintptr_t end = reinterpret_cast<uintptr_t>(d.src) + (size_t)(r1 - 1) * d.pitch + (size_t)d.W * d.cin;
+    const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (end + 15) & ~(uintptr_t)15;
+    const uint32_t bytes = (uint32_t)(a1 - a0);
+    mbar_expect_tx(&bars[s], bytes);
+    tma_load_1d(raw + (size_t)s * d.stage_bytes, reinterpret_cast<const void*>(a0), bytes, &bars[s]);
+  };
+
+  if (tid == 0) {
+    for (int s = 0; s < d.nst; s++) mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int i = tid; i < C * 256 * elem / 4; i += nthreads)
+    reinterpret_cast<uint32_t*>(s_lut)[i] = reinterpret_cast<const uint32_t*>(lut)[i];
+  __syncthreads();
+  if (tid == 0)
+    for (int g = g_first; g <= g_last && g < g_first + d.nst; g++) issue(g);
+
+  // ---- per-thread horizontal coefficients (registers) -------------------------------------------
+  const int xx = tid;
+  uint32_t kc[NW][3];
+  int w0 = 0;
+  if (xx < out_w) {
+    w0 = pool[d.hw0_off + xx];
+    const int32_t* hc = pool + d.hc_off + (size_t)xx * NW * 3;
+#pragma unroll
+    for (int j = 0; j < NW; j++) {
+      kc[j][0] = hc[j * 3 + 0]; kc[j][1] = hc[j * 3 + 1]; kc[j][2] = hc[j * 3 + 2];
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < NW; j++) { kc[j][0] = 0; kc[j][1] = 0; kc[j][2] = 0; }
+  }
+
+  const int nwords = (d.W + 3) >> 2;
+  const bool nchw = layout == TCB_LAYOUT_NCHW;
+  const bool vec4 = dst_aligned16 && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));
+  const int32_t* vg = pool + d.vg_off;
+  uint8_t* dimg = dst + (size_t)img * C * out_h * out_w * elem;
+  int yy_next = yy0;
+
+  for (int g = g_first; g <= g_last; g++) {
+    const int s = (g - g_first) % d.nst;
+    mbar_wait(&bars[s], ((g - g_first) / d.nst) & 1);
+    // ---- de-interleave stage s -> P4 ------------------------------------------------------------
+    {
+      const uint8_t* stage = raw + (size_t)s * d.stage_bytes;
+      const uint32_t lead = (uint32_t)((reinterpret_cast<uintptr_t>(d.src) + (size_t)(4 * g) * d.pitch) & 15);
+      const int nrows = min(4, d.H - 4 * g);
+      if (d.aligned4 && d.cin == 3 && C == 3) {
+        for (int w = tid; w < nwords; w += nthreads) {
+          uint32_t R[4], G[4], B[4];
+#pragma unroll
+          for (int r = 0; r < 4; r++) {
+            uint32_t x0 = 0, x1 = 0, x2 = 0;
+            if (r < nrows) {
+              const uint32_t* rp = reinterpret_cast<const uint32_t*>(stage + lead + (size_t)r * d.pitch) + 3 * w;
+              x0 = rp[0]; x1 = rp[1]; x2 = rp[2];  // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+            }
+            R[r] = __byte_perm(__byte_perm(x0, x1, 0x0630), x2, 0x5210);
+            G[r] = __byte_perm(__byte_perm(x0, x1, 0x0741), x2, 0x6210);
+            B[r] = __byte_perm(__byte_perm(x0, x1, 0x0052), x2, 0x7410);
+          }
+          P4[w] = make_uint4(R[0], R[1], R[2], R[3]);
+          P4[(C > 1 ? 1 : 0) * d.wq + w] = make_uint4(G[0], G[1], G[2], G[3]);
+          P4[(C > 2 ? 2 : 0) * d.wq + w] = make_uint4(B[0], B[1], B[2], B[3]);
+        }
+      } else if (d.aligned4 && d.cin == 1 && C == 1) {
+        for (int w = tid; w < nwords; w += nthreads) {
+          uint32_t v[4];
+#pragma unroll
+          for (int r = 0; r < 4; r++)
+            v[r] = r < nrows ? reinterpret_cast<const uint32_t*>(stage + lead + (size_t)r * d.pitch)[w] : 0u;
+          P4[w] = make_uint4(v[0], v[1], v[2], v[3]);
+        }
+      } else {  // any channel conversion / unaligned rows: byte-wise
+        for (int i = tid; i < nwords * C; i += nthreads) {
+          const int ch = i / nwords, w = i - ch * nwords;
+          uint32_t v[4];
+#pragma unroll
+          for (int r = 0; r < 4; r++) {
+            uint32_t word = 0;
+            if (r < nrows) {
+              const uint8_t* row = stage + lead + (size_t)r * d.pitch;
+#pragma unroll
+              for (int b = 0; b < 4; b++) {
+                const int x = 4 * w + b;
+                if (x < d.W) word |= fetch_conv(row, d.cin, C, x, ch) << (8 * b);
+              }
+            }
+            v[r] = word;
+          }
+          P4[ch * d.wq + w] = make_uint4(v[0], v[1], v[2], v[3]);
+        }
+      }
+    }
+    __syncthreads();  // P4 complete; stage s fully consumed
+    if (tid == 0 && g + d.nst <= g_last) issue(g + d.nst);
+
+    // ---- horizontal pass: 4 rows x C channels per thread ---------------------------------------
+    if (xx < out_w) {
+      uint32_t* slot = tmp4 + (size_t)(g % ng) * L;
+#pragma unroll
+      for (int ch = 0; ch < C; ch++) {
+        uint32_t a[4][3];
+#pragma unroll
+        for (int r = 0; r < 4; r++) { a[r][0] = 0; a[r][1] = 0; a[r][2] = 0; }
+        const uint4* p = P4 + ch * d.wq + w0;
+#pragma unroll
+        for (int j = 0; j < NW; j++) {
+          const uint4 v = p[j];
+          a[0][0] = __dp4a(v.x, kc[j][0], a[0][0]); a[0][1] = __dp4a(v.x, kc[j][1], a[0][1]); a[0][2] = __dp4a(v.x, kc[j][2], a[0][2]);
+          a[1][0] = __dp4a(v.y, kc[j][0], a[1][0]); a[1][1] = __dp4a(v.y, kc[j][1], a[1][1]); a[1][2] = __dp4a(v.y, kc[j][2], a[1][2]);
+          a[2][0] = __dp4a(v.z, kc[j][0], a[2][0]); a[2][1] = __dp4a(v.z, kc[j][1], a[2][1]); a[2][2] = __dp4a(v.z, kc[j][2], a[2][2]);
+          a[3][0] = __dp4a(v.w, kc[j][0], a[3][0]); a[3][1] = __dp4a(v.w, kc[j][1], a[3][1]); a[3][2] = __dp4a(v.w, kc[j][2], a[3][2]);
+        }
+        uint32_t packed = 0;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+          const uint32_t acc = (1u << (kPrecisionBits - 1)) + a[r][0] + (a[r][1] << 8) + (a[r][2] << 16);
+          packed |= min(acc >> kPrecisionBits, 255u) << (8 * r);
+        }
+        slot[nchw ? ch * out_w + xx : xx * C + ch] = packed;
+      }
+    }
+    __syncthreads();  // tmp4 slot visible; P4 free for the next group
+
+    // ---- vertical pass for every output row whose last group has arrived -----------------------
+    while (yy_next < yy1 && vg[2 * yy_next + 1] <= g) {
+      const int yy = yy_next;
+      const int gv0 = vg[2 * yy];
+      const int32_t* vc = pool + d.vc_off + (size_t)yy * d.nwv * 3;
+      if (vec4) {
+        for (int u4 = tid; u4 < L / 4; u4 += nthreads) {
+          const int i0 = 4 * u4;
+          uint32_t a[4][3];
+#pragma unroll
+          for (int v = 0; v < 4; v++) { a[v][0] = 0; a[v][1] = 0; a[v][2] = 0; }
+          for (int j = 0; j < d.nwv; j++) {
+            const uint32_t k0 = vc[3 * j], k1 = vc[3 * j + 1], k2 = vc[3 * j + 2];
+            const uint4 px = *reinterpret_cast<const uint4*>(tmp4 + (size_t)((gv0 + j) % ng) * L + i0);
+            a[0][0] = __dp4a(px.x, k0, a[0][0]); a[0][1] = __dp4a(px.x, k1, a[0][1]); a[0][2] = __dp4a(px.x, k2, a[0][2]);
+            a[1][0] = __dp4a(px.y, k0, a[1][0]); a[1][1] = __dp4a(px.y, k1, a[1][1]); a[1][2] = __dp4a(px.y, k2, a[1][2]);
+            a[2][0] = __dp4a(px.z, k0, a[2][0]); a[2][1] = __dp4a(px.z, k1, a[2][1]); a[2][2] = __dp4a(px.z, k2, a[2][2]);
+            a[3][0] = __dp4a(px.w, k0, a[3][0]); a[3][1] = __dp4a(px.w, k1, a[3][1]); a[3][2] = __dp4a(px.w, k2, a[3][2]);
+          }
+          uint32_t u[4];
+#pragma unroll
+          for (int v = 0; v < 4; v++) {
+            const uint32_t acc = (1u << (kPrecisionBits - 1)) + a[v][0] + (a[v][1] << 8) + (a[v][2] << 16);
+            u[v] = min(acc >> kPrecisionBits, 255u);
+          }
+          // destination element index of word i0 (4 consecutive elements share a line)
+          size_t e0;
+          int ch0, chs;
+          if (nchw) {
+            const int ch = i0 / out_w, x = i0 - ch * out_w;
+            e0 = ((size_t)ch * out_h + yy) * out_w + x; ch0 = ch; chs = 0;
+          } else {
+            e0 = (size_t)yy * L + i0; ch0 = i0 % C; chs = 1;
+          }
+          int chv[4];
+#pragma unroll
+          for (int v = 0; v < 4; v++) { int c2 = ch0 + chs * v; chv[v] = chs ? c2 % C : c2; }
+          if (elem == 4) {
+            const uint32_t* l32 = reinterpret_cast<const uint32_t*>(s_lut);
+            st_global_v4(dimg + e0 * 4, l32[chv[0] * 256 + u[0]], l32[chv[1] * 256 + u[1]],
+                         l32[chv[2] * 256 + u[2]], l32[chv[3] * 256 + u[3]]);
+          } else if (elem == 2) {
+            const uint16_t* l16 = reinterpret_cast<const uint16_t*>(s_lut);
+            const uint32_t lo = l16[chv[0] * 256 + u[0]] | ((uint32_t)l16[chv[1] * 256 + u[1]] << 16);
+            const uint32_t hi = l16[chv[2] * 256 + u[2]] | ((uint32_t)l16[chv[3] * 256 + u[3]] << 16);
+            st_global_v2(dimg + e0 * 2, lo, hi);
+          } else if (elem == 1) {
+            const uint32_t w = s_lut[chv[0] * 256 + u[0]] | ((uint32_t)s_lut[chv[1] * 256 + u[1]] << 8) |
+                               ((uint32_t)s_lut[chv[2] * 256 + u[2]] << 16) | ((uint32_t)s_lut[chv[3] * 256 + u[3]] << 24);
+            *reinterpret_cast<uint32_t*>(dimg + e0) = w;
+          } else {
+            const uint2* l64 = reinterpret_cast<const uint2*>(s_lut);
+            const uint2 q0 = l64[chv[0] * 256 + u[0]], q1 = l64[chv[1] * 256 + u[1]];
+            const uint2 q2 = l64[chv[2] * 256 + u[2]], q3 = l64[chv[3] * 256 + u[3]];
+            st_global_v4(dimg + e0 * 8, q0.x, q0.y, q1.x, q1.y);
+            st_global_v4(dimg + e0 * 8 + 16, q2.x, q2.y, q3.x, q3.y);
+          }
+        }
+      } else {
+        for (int i = tid; i < L; i += nthreads) {
+          uint32_t a0 = 0, a1 = 0, a2 = 0;
+          for (int j = 0; j < d.nwv; j++) {
+            const uint32_t px = tmp4[(size_t)((gv0 + j) % ng) * L + i];
+            a0 = __dp4a(px, (uint32_t)vc[3 * j], a0); a1 = __dp4a(px, (uint32_t)vc[3 * j + 1], a1);
+            a2 = __dp4a(px, (uint32_t)vc[3 * j + 2], a2);
+          }
+          const uint32_t acc = (1u << (kPrecisionBits - 1)) + a0 + (a1 << 8) + (a2 << 16);
+          const uint32_t u = min(acc >> kPrecisionBits, 255u);
+          size_t e;
+          int ch;
+          if (nchw) { ch = i / out_w; e = ((size_t)ch * out_h + yy) * out_w + (i - ch * out_w); }
+          else { ch = i % C; e = (size_t)yy * L + i; }
+          const uint8_t* le = s_lut + ((size_t)ch * 256 + u) * elem;
+          if (elem == 4) reinterpret_cast<uint32_t*>(dimg)[e] = *reinterpret_cast<const uint32_t*>(le);
+          else if (elem == 2) reinterpret_cast<uint16_t*>(dimg)[e] = *reinterpret_cast<const uint16_t*>(le);
+          else if (elem == 1) dimg[e] = *le;
+          else reinterpret_cast<uint64_t*>(dimg)[e] = *reinterpret_cast<const uint64_t*>(le);
+        }
+      }
+      yy_next++;
+    }
+    // the next iteration's de-interleave only touches P4/raw; its __syncthreads orders this
+    // vertical pass before the next horizontal pass overwrites a tmp4 slot
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------
+// Packs Pillow's int32 coefficients of one axis into dp4a byte planes on the 4-sample word grid.
+// Returns the words per output (max over outputs); first[xx] = first word index.
+static int pack_axis(const std::vector<int32_t>& bounds, const std::vector<int32_t>& kk, int ksize, int out,
+                     int force_nw, std::vector<int32_t>& packed, std::vector<int32_t>& first,
+                     std::vector<int32_t>* last = nullptr) {
+  int nw = 1;
+  for (int o = 0; o < out; o++) {
+    const int xmin = bounds[2 * o], n = bounds[2 * o + 1];
+    nw = std::max(nw, ((xmin + n - 1) >> 2) - (xmin >> 2) + 1);
+  }
+  if (force_nw > 0) {
+    if (force_nw < nw) return -nw;
+    nw = force_nw;
+  }
+  packed.assign((size_t)out * nw * 3, 0);
+  first.assign(out, 0);
+  if (last) last->assign(out, 0);
+  for (int o = 0; o < out; o++) {
+    const int xmin = bounds[2 * o], n = bounds[2 * o + 1];
+    const int w0 = xmin >> 2;
+    first[o] = w0;
+    if (last) (*last)[o] = (xmin + n - 1) >> 2;
+    for (int t = 0; t < n; t++) {
+      const uint32_t k = (uint32_t)kk[(size_t)o * ksize + t];
+      const int pos = xmin + t - 4 * w0, j = pos >> 2, b = pos & 3;
+      for (int p = 0; p < 3; p++) {
+        uint32_t& word = reinterpret_cast<uint32_t&>(packed[((size_t)o * nw + j) * 3 + p]);
+        word |= ((k >> (8 * p)) & 0xffu) << (8 * b);
+      }
+    }
+  }
+  return nw;
+}
+
+static int nw_class(int nw) {
+  for (int c : kNwClasses)
+    if (nw <= c) return c;
+  return -1;
+}
+
+struct FusedGeom {
+  int nw_class, nwv, wq, stage_bytes, nst, threads;
+  size_t smem;
+};
+
+static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc& d, FusedGeom* g) {
+  if (d.p1_axis != AXIS_H || d.p2_axis != AXIS_V) return false;
+  if (!((d.cin == 3 && c == 3) || (d.cin == 1 && c == 1) || (d.cin == 4 && c == 3) ||
+        ((d.cin == 3 || d.cin == 4) && c == 1)))
+    return false;
+  if (out_w > kFusedMaxThreads) return false;
+  std::vector<int32_t> b, k, packed, first;
+  const int ksh = compute_axis_coeffs(d.W, out_w, b, k);
+  const int nw = pack_axis(b, k, ksh, out_w, 0, packed, first);
+  const int cls = nw_class(nw);
+  if (cls < 0) return false;
+  const int ksv = compute_axis_coeffs(d.H, out_h, b, k);
+  const int nwv = pack_axis(b, k, ksv, out_h, 0, packed, first);
+  if (nwv > 24) return false;
+  g->nw_class = cls; g->nwv = nwv;
+  g->wq = ((d.W + 3) >> 2) + cls + 1;
+  g->stage_bytes = (int)round_up((uint64_t)4 * d.pitch + 48, 128);
+  g->threads = std::max(128, (int)round_up(out_w, 32));
+  const size_t fixed = 64 + round_up((uint64_t)c * 256 * elem, 128) + (size_t)c * g->wq * 16 +
+                       (size_t)(nwv + 1) * out_w * c * 4 + 128;
+  g->nst = 3;
+  g->smem = fixed + (size_t)g->nst * g->stage_bytes;
+  if (g->smem > 110 * 1024) {  // prefer two resident CTAs per SM over a third stage
+    g->nst = 2;
+    g->smem = fixed + (size_t)g->nst * g->stage_bytes;
+  }
+  return g->smem <= kFusedMaxSmem;
+}
+
+struct FusedPlan {
+  std::vector<FusedDesc> desc;                 // one per plan image (valid where fused)
+  std::map<int, std::vector<int32_t>> work;    // nw class -> (image, first output row) pairs
+  std::map<int, size_t> smem;                  // nw class -> dynamic shared memory
+  std::map<int, int> threads;
+  FusedDesc* d_desc = nullptr;
+  int32_t* d_work = nullptr;
+  std::map<int, size_t> work_off;
+  int32_t* d_pool = nullptr;
+};
+
+static std::map<const Plan*, FusedPlan*>& registry() {
+  static std::map<const Plan*, FusedPlan*> r;
+  return r;
+}
+
+bool fused_supported(const Plan& p, const ImgDesc& d, int* band_rows, size_t* smem_bytes) {
+  FusedGeom g;
+  if (!fused_geometry(p.c, p.out_h, p.out_w, p.elem, d, &g)) return false;
+  // bands: enough CTAs to fill the GPU a few times over, but keep the halo overhead small
+  const int sms = sm_count(p.device);
+  const long long target = 8ll * sms;
+  int rows = (int)std::min<long long>(p.out_h, std::max<long long>(8, ((long long)p.out_h * p.n + target - 1) / target));
+  const int nb = (p.out_h + rows - 1) / rows;
+  rows = (p.out_h + nb - 1) / nb;
+  *band_rows = rows;
+  *smem_bytes = g.smem;
+  return true;
+}
+
+template <int NW>
+static int launch_class(const Plan& p, const FusedPlan& fp, int cls, void* dst, cudaStream_t s) {
+  const auto it = fp.work.find(cls);
+  const int ctas = (int)(it->second.size() / 2);
+  const size_t smem = fp.smem.at(cls);
+  const int threads = fp.threads.at(cls);
+  const int32_t* work = fp.d_work + fp.work_off.at(cls);
+  const int al = (reinterpret_cast<uintptr_t>(dst) % 16 == 0) ? 1 : 0;
+  if (p.c == 3) {
+    TCB_CUDA(cudaFuncSetAttribute(k_preprocess_fused<NW, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_preprocess_fused<NW, 3><<<ctas, threads, smem, s>>>(fp.d_desc, work, fp.d_pool, p.d_lut, (uint8_t*)dst, p.out_h,
+                                                          p.out_w, p.layout, p.elem, al);
+  } else {
+    TCB_CUDA(cudaFuncSetAttribute(k_preprocess_fused<NW, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_preprocess_fused<NW, 1><<<ctas, threads, smem, s>>>(fp.d_desc, work, fp.d_pool, p.d_lut, (uint8_t*)dst, p.out_h,
+                                                          p.out_w, p.layout, p.elem, al);
+  }
+  count_launch();
+  return TCB_OK;
+}
+
+int fused_prepare(Plan& p) {
+  FusedPlan* fp = new FusedPlan();
+  fp->desc.resize(p.n);
+  std::vector<int32_t> pool;
+  std::map<std::pair<int, int>, std::array<int32_t, 3>> htab;   // (W, class) -> hc_off, hw0_off, nw
+  std::map<int, std::array<int32_t, 4>> vtab;                    // H -> vc_off, vg_off, vb_off, nwv
+  auto align4 = [&]() { while (pool.size() % 4) pool.push_back(0); };
+  for (int i = 0; i < p.n; i++) {
+    const ImgDesc& d = p.h_desc[i];
+    if (!d.fused) continue;
+    FusedGeom g;
+    fused_geometry(p.c, p.out_h, p.out_w, p.elem, d, &g);
+    FusedDesc& f = fp->desc[i];
+    f.src = d.src; f.W = d.W; f.H = d.H; f.pitch = d.pitch; f.cin = d.cin;
+    f.nw = g.nw_class; f.nwv = g.nwv; f.band_rows = d.band_rows; f.wq = g.wq;
+    f.stage_bytes = g.stage_bytes; f.nst = g.nst;
+    f.aligned4 = (reinterpret_cast<uintptr_t>(d.src) % 4 == 0) && (d.pitch % 4 == 0);
+    auto hk = std::make_pair(d.W, g.nw_class);
+    if (!htab.count(hk)) {
+      std::vector<int32_t> b, k, packed, first;
+      const int ks = compute_axis_coeffs(d.W, p.out_w, b, k);
+      pack_axis(b, k, ks, p.out_w, g.nw_class, packed, first);
+      std::array<int32_t, 3> e;
+      align4(); e[0] = (int32_t)pool.size(); pool.insert(pool.end(), packed.begin(), packed.end());
+      align4(); e[1] = (int32_t)pool.size(); pool.insert(pool.end(), first.begin(), first.end());
+      e[2] = g.nw_class;
+      htab[hk] = e;
+    }
+    if (!vtab.count(d.H)) {
+      std::vector<int32_t> b, k, packed, first, last;
+      const int ks = compute_axis_coeffs(d.H, p.out_h, b, k);
+      const int nwv = pack_axis(b, k, ks, p.out_h, 0, packed, first, &last);
+      std::array<int32_t, 4> e;
+      align4(); e[0] = (int32_t)pool.size(); pool.insert(pool.end(), packed.begin(), packed.end());
+      align4(); e[1] = (int32_t)pool.size();
+      for (int o = 0; o < p.out_h; o++) { pool.push_back(first[o]); pool.push_back(last[o]); }
+      align4(); e[2] = (int32_t)pool.size(); pool.insert(pool.end(), b.begin(), b.end());
+      e[3] = nwv;
+      vtab[d.H] = e;
+    }
+    f.hc_off = htab[hk][0]; f.hw0_off = htab[hk][1];
+    f.vc_off = vtab[d.H][0]; f.vg_off = vtab[d.H][1]; f.vb_off = vtab[d.H][2];
+    auto& wl = fp->work[g.nw_class];
+    for (int y0 = 0; y0 < p.out_h; y0 += d.band_rows) { wl.push_back(i); wl.push_back(y0); }
+    fp->smem[g.nw_class] = std::max(fp->smem[g.nw_class], g.smem);
+    fp->threads[g.nw_class] = g.threads;
+  }
+  std::vector<int32_t> allwork;
+  for (auto& kv : fp->work) {
+    fp->work_off[kv.first] = allwork.size();
+    allwork.insert(allwork.end(), kv.second.begin(), kv.second.end());
+  }
+  if (pool.empty()) pool.push_back(0);
+  cudaError_t e = cudaMalloc((void**)&fp->d_desc, sizeof(FusedDesc) * p.n);
+  if (e == cudaSuccess) e = cudaMemcpy(fp->d_desc, fp->desc.data(), sizeof(FusedDesc) * p.n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&fp->d_work, allwork.size() * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemcpy(fp->d_work, allwork.data(), allwork.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&fp->d_pool, pool.size() * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemcpy(fp->d_pool, pool.data(), pool.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    cudaFree(fp->d_desc); cudaFree(fp->d_work); cudaFree(fp->d_pool);
+    delete fp;
+    return set_error(TCB_ERR_NOMEM, "fused preprocess set-up failed: %s", cudaGetErrorString(e));
+  }
+  registry()[&p] = fp;
+  return TCB_OK;
+}
+
+void fused_release(const Plan& p) {
+  auto it = registry().find(&p);
+  if (it == registry().end()) return;
+  cudaFree(it->second->d_desc); cudaFree(it->second->d_work); cudaFree(it->second->d_pool);
+  delete it->second;
+  registry().erase(it);
+}
+
+int fused_update_sources(const Plan& p, cudaStream_t s) {
+  auto it = registry().find(&p);
+  if (it == registry().end()) return TCB_OK;
+  FusedPlan* fp = it->second;
+  for (int i = 0; i < p.n; i++)
+    if (p.h_desc[i].fused) { fp->desc[i].src = p.h_desc[i].src; fp->desc[i].pitch = p.h_desc[i].pitch; }
+  TCB_CUDA(cudaMemcpyAsync(fp->d_desc, fp->desc.data(), sizeof(FusedDesc) * p.n, cudaMemcpyHostToDevice, s));
+  return TCB_OK;
+}
+
+int fused_launch(const Plan& p, void* dst, cudaStream_t s) {
+  auto it = registry().find(&p);
+  if (it == registry().end()) return set_error(TCB_ERR_INTERNAL, "fused plan missing");
+  const FusedPlan& fp = *it->second;
+  for (auto& kv : fp.work) {
+    int rc = TCB_OK;
+    switch (kv.first) {
+      case 2: rc = launch_class<2>(p, fp, 2, dst, s); break;
+      case 3: rc = launch_class<3>(p, fp, 3, dst, s); break;
+      case 4: rc = launch_class<4>(p, fp, 4, dst, s); break;
+      case 6: rc = launch_class<6>(p, fp, 6, dst, s); break;
+      case 8: rc = launch_class<8>(p, fp, 8, dst, s); break;
+      case 12: rc = launch_class<12>(p, fp, 12, dst, s); break;
+      case 16: rc = launch_class<16>(p, fp, 16, dst, s); break;
+      default: rc = set_error(TCB_ERR_INTERNAL, "bad coefficient class %d", kv.first);
+    }
+    if (rc) return rc;
+  }
+  return TCB_OK;
 }
 
 }  // namespace tcb
