@@ -167,6 +167,32 @@ int TcbBytesSerialize(int device_id, const void* payload_dev, const void* length
                       void* workspace_dev, uint64_t workspace_bytes, uint64_t* total_dev,
                       uint64_t* total_host, void* stream);
 
+/* Same result as TcbBytesSerialize, for callers that must not allocate. No counterpart in the
+ * reference (its serialiser is a host-side Python loop; there is nothing to bind this to).
+ *
+ * Who needs it: code that runs while the device's memory is already spoken for or while an
+ * allocation would stall it - a serving process that handed its whole HBM budget to its own
+ * arena, a request handler on a latency budget (cudaMalloc takes a driver-wide lock and
+ * synchronises the device), a callback or library hook that is simply not allowed to call the
+ * allocator. TcbBytesSerialize asks such a caller for a workspace it cannot create.
+ *
+ * Here the scan scratch is a fixed array inside the library image instead (131 144 bytes of
+ * device memory, present on every GPU that loads libtcb200.so for the life of the process), so
+ * the call takes only inputs and outputs and calls no cudaMalloc / cudaFree / allocating
+ * library routine.
+ *   - Limit: n_elements <= 16 777 216 per call (one status word per 1024 elements); more is
+ *     refused with TCB_ERR_OUT_OF_RANGE and a message that says so.
+ *   - The first call on each device looks up the array's device address (a one-off set-up
+ *     step under that device); make that first call before starting any stream capture.
+ *   - All calls on a device share the one array. Each call clears the part it uses on `stream`
+ *     before its kernel runs, so back-to-back calls on one stream are fine; two calls whose GPU
+ *     work can overlap (different streams, different threads) race on it and must be ordered by
+ *     the caller.
+ * Arguments as TcbBytesSerialize, minus the workspace and total_dev. */
+int TcbBytesSerializeNoAlloc(int device_id, const void* payload_dev, const void* lengths_dev,
+                             int length_size, uint64_t n_elements, void* dst_dev,
+                             uint64_t dst_capacity, uint64_t* total_host, void* stream);
+
 /* Fixed-width rows (numpy `S<k>` arrays: n rows of `width` bytes, element = row with trailing
  * NULs stripped, utils/__init__.py:239). Same outputs as TcbBytesSerialize. */
 int TcbBytesSerializeFixedWidth(int device_id, const void* rows_dev, uint32_t width,

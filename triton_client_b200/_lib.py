@@ -34,7 +34,7 @@ EXPORTS = [
     "TcbPreprocessPlanCreate", "TcbPreprocessPlanRun", "TcbPreprocessPlanInfo",
     "TcbPreprocessPlanDestroy", "TcbResampleCoeffs",
     "TcbBytesSerializeWorkspace", "TcbBytesDeserializeWorkspace", "TcbBytesSerialize",
-    "TcbBytesSerializeFixedWidth", "TcbBytesDeserialize",
+    "TcbBytesSerializeFixedWidth", "TcbBytesDeserialize", "TcbBytesSerializeNoAlloc",
 ]
 
 
@@ -101,6 +101,8 @@ _sig("TcbBytesDeserializeWorkspace", c_uint64, [c_uint64])
 _sig("TcbBytesSerialize", c_int,
      [c_int, c_void_p, c_void_p, c_int, c_uint64, c_void_p, c_uint64, c_void_p, c_uint64,
       c_void_p, POINTER(c_uint64), c_void_p])
+_sig("TcbBytesSerializeNoAlloc", c_int,
+     [c_int, c_void_p, c_void_p, c_int, c_uint64, c_void_p, c_uint64, POINTER(c_uint64), c_void_p])
 _sig("TcbBytesSerializeFixedWidth", c_int,
      [c_int, c_void_p, c_uint32, c_uint64, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p,
       POINTER(c_uint64), c_void_p])

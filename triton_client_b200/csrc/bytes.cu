@@ -757,3 +757,60 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// Serialise without allocating anything (see TcbBytesSerializeNoAlloc in include/tcb200.h)
+// =================================================================================================
+#include <mutex>
+
+namespace tcb {
+
+// Most elements one call may serialise. The look-back scan needs one 64-bit status word per tile
+// of 1024 elements plus an 8-word header, so this bounds the scratch below at 131 144 bytes.
+constexpr uint64_t kNoAllocMaxElements = 16ull << 20;
+constexpr uint64_t kNoAllocScratchWords = WS_HEADER_WORDS + kNoAllocMaxElements / kSerTile + 1;
+
+// The scan scratch of the no-alloc entry point. It is part of the library image: every GPU that
+// loads libtcb200.so carries these 128 KiB from module load until the process exits, whether or
+// not the entry point is ever called. In HOST code this name is only a stand-in for the symbol;
+// the device address comes from cudaGetSymbolAddress below and that is what kernels receive.
+static __device__ __align__(256) unsigned long long g_noalloc_scan_scratch[kNoAllocScratchWords];
+
+// Device address of the array above, looked up once per device with that device current.
+static int noalloc_scratch_for(int device_id, unsigned long long** out) {
+  static std::mutex mu;
+  static unsigned long long* addr[64] = {nullptr};
+  TCB_CHECK_ARG(device_id >= 0 && device_id < 64, "TcbBytesSerializeNoAlloc: bad device %d", device_id);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[device_id]) {
+    TCB_DEVICE_GUARD(device_id);
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scan_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return set_error(TCB_ERR_CUDA, "TcbBytesSerializeNoAlloc: cudaGetSymbolAddress failed on device %d: %s",
+                       device_id, cudaGetErrorString(e));
+    addr[device_id] = static_cast<unsigned long long*>(p);
+  }
+  *out = addr[device_id];
+  return TCB_OK;
+}
+
+}  // namespace tcb
+
+extern "C" int TcbBytesSerializeNoAlloc(int device_id, const void* payload_dev, const void* lengths_dev,
+                                        int length_size, uint64_t n_elements, void* dst_dev,
+                                        uint64_t dst_capacity, uint64_t* total_host, void* stream) {
+  if (n_elements > tcb::kNoAllocMaxElements)
+    return tcb::set_error(TCB_ERR_OUT_OF_RANGE,
+                          "TcbBytesSerializeNoAlloc: %llu elements exceed the built-in scratch, which covers at "
+                          "most %llu elements per call; split the tensor or use TcbBytesSerialize with a "
+                          "caller-provided workspace",
+                          (unsigned long long)n_elements, (unsigned long long)tcb::kNoAllocMaxElements);
+  unsigned long long* scratch = nullptr;
+  const int rc = tcb::noalloc_scratch_for(device_id, &scratch);
+  if (rc) return rc;
+  // serialize_common zeroes the part of the scratch this call uses (header + one status word per
+  // tile) on `stream` before the kernel, so whatever the previous call left behind is gone.
+  return serialize_common(device_id, payload_dev, lengths_dev, length_size, false, 0, n_elements, dst_dev,
+                          dst_capacity, scratch, tcb::kNoAllocScratchWords * 8, nullptr, total_host, stream);
+}
