@@ -20,6 +20,7 @@
 // HBM traffic is the source once (+ the band halo) and the output once.
 #include <algorithm>
 #include <array>
+#include <cstdlib>
 #include <map>
 
 #include "preprocess.cuh"
@@ -51,6 +52,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
       "r"(parity)
       : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// Wait with a time bound: a protocol bug becomes a trapped kernel (an error code on the host)
+// instead of a hung GPU.
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  const long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (done) return;
+    __nanosleep(40);  // waiting warps must not eat the issue slots of working warps
+    if (clock64() - t0 > 8000000000ll) __trap();
+  }
 }
 // 1-D TMA: global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
@@ -94,9 +116,17 @@ __device__ __forceinline__ uint32_t fetch_conv(const uint8_t* row, int cin, int 
   return (q[0] * 19595u + q[1] * 38470u + q[2] * 7471u + 0x8000u) >> 16;
 }
 
-// NW: coefficient words per output column; C: output channels.
-template <int NW, int C>
-__global__ void __launch_bounds__(kFusedMaxThreads, 1)
+// Physical granule index of logical granule w in a P4 plane: one granule of padding after every
+// 8. Output columns that are ~2 granules apart (1080p -> 224) then fall into distinct bank groups
+// instead of colliding pairwise (measured: 32 % of all shared-memory wavefronts were conflicts).
+__host__ __device__ __forceinline__ int p4_phys(int w) { return w + (w >> 3); }
+
+// NW: coefficient words per output column; C: output channels; BIG: more than 256 output columns
+// (one CTA per SM). Software-pipelined: in phase i every thread (a) de-interleaves row group i+1
+// into the other P4 buffer, (b) runs the horizontal pass of group i, (c) runs the vertical pass
+// of the output rows completed by group i-1; one __syncthreads per phase.
+template <int NW, int C, bool BIG>
+__global__ void __launch_bounds__(BIG ? 512 : 256, BIG ? 1 : 2)
 k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restrict__ work,
                    const int32_t* __restrict__ pool, const uint8_t* __restrict__ lut,
                    uint8_t* __restrict__ dst, int out_h, int out_w, int layout, int elem,
@@ -106,23 +136,23 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   const FusedDesc d = descs[img];
   const int tid = threadIdx.x, nthreads = blockDim.x;
   const int yy1 = min(yy0 + d.band_rows, out_h);
-  const int L = out_w * C;  // words per tmp4 slot / elements per output row
-  const int ng = d.nwv + 1;
+  const int L = out_w * C;   // words per tmp4 slot = elements per output row
+  const int ng = d.nwv + 1;  // ring slots
+  const int wqp = d.wq;      // physical granules per P4 plane (padding included)
 
-  // ---- shared memory carve-up -------------------------------------------------------------------
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                   // [nst]
-  uint8_t* s_lut = smem + 64;                                           // C*256*elem
-  uint8_t* raw = smem + 64 + ((C * 256 * elem + 127) & ~127);           // nst stages
-  uint4* P4 = reinterpret_cast<uint4*>(raw + (size_t)d.nst * d.stage_bytes);  // [C][wq]
-  uint32_t* tmp4 = reinterpret_cast<uint32_t*>(P4 + (size_t)C * d.wq);  // [ng][L]
+  // shared memory: barriers | raw stages (2) | P4 x2 | tmp4 ring
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  uint8_t* raw = smem + 64;
+  uint4* P4 = reinterpret_cast<uint4*>(raw + (size_t)2 * d.stage_bytes);  // [2][C][wqp]
+  uint32_t* tmp4 = reinterpret_cast<uint32_t*>(P4 + (size_t)2 * C * wqp); // [ng][L]
 
-  // source row groups this band needs
   const int32_t* vb = pool + d.vb_off;
-  const int ys = vb[2 * yy0], ye = vb[2 * (yy1 - 1)] + vb[2 * (yy1 - 1) + 1];  // rows [ys, ye)
+  const int ys = vb[2 * yy0], ye = vb[2 * (yy1 - 1)] + vb[2 * (yy1 - 1) + 1];  // source rows [ys, ye)
   const int g_first = ys >> 2, g_last = (ye - 1) >> 2;
+  const int n_groups = g_last - g_first + 1;
 
-  auto issue = [&](int g) {  // thread 0: TMA for row group g into its stage
-    const int s = (g - g_first) % d.nst;
+  auto issue = [&](int i) {  // thread 0: TMA for the i-th row group of this band into stage i & 1
+    const int g = g_first + i, s = i & 1;
     const int r1 = min(4 * g + 4, d.H);
     const uintptr_t start = reinterpret_cast<uintptr_t>(d.src) + (size_t)(4 * g) * d.pitch;
     const uintptr_t end = reinterpret_cast<uintptr_t>(d.src) + (size_t)(r1 - 1) * d.pitch + (size_t)d.W * d.cin;
@@ -133,208 +163,245 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   };
 
   if (tid == 0) {
-    for (int s = 0; s < d.nst; s++) mbar_init(&bars[s], 1);
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (int i = tid; i < C * 256 * elem / 4; i += nthreads)
-    reinterpret_cast<uint32_t*>(s_lut)[i] = reinterpret_cast<const uint32_t*>(lut)[i];
   __syncthreads();
-  if (tid == 0)
-    for (int g = g_first; g <= g_last && g < g_first + d.nst; g++) issue(g);
+  if (tid == 0) {
+    issue(0);
+    if (n_groups > 1) issue(1);
+  }
 
-  // ---- per-thread horizontal coefficients (registers) -------------------------------------------
+  // ---- per-thread constants ------------------------------------------------------------------------
+  const bool nchw = layout == TCB_LAYOUT_NCHW;
   const int xx = tid;
   uint32_t kc[NW][3];
-  int w0 = 0;
+  int poff[NW];  // physical granule offsets of this column's NW source words
+#pragma unroll
+  for (int j = 0; j < NW; j++) { kc[j][0] = 0; kc[j][1] = 0; kc[j][2] = 0; poff[j] = 0; }
   if (xx < out_w) {
-    w0 = pool[d.hw0_off + xx];
+    const int w0 = pool[d.hw0_off + xx];
     const int32_t* hc = pool + d.hc_off + (size_t)xx * NW * 3;
 #pragma unroll
     for (int j = 0; j < NW; j++) {
       kc[j][0] = hc[j * 3 + 0]; kc[j][1] = hc[j * 3 + 1]; kc[j][2] = hc[j * 3 + 2];
+      poff[j] = p4_phys(w0 + j);
     }
-  } else {
-#pragma unroll
-    for (int j = 0; j < NW; j++) { kc[j][0] = 0; kc[j][1] = 0; kc[j][2] = 0; }
   }
-
+  const int tmp_idx0 = nchw ? xx : xx * C;      // + ch * (nchw ? out_w : 1)
+  const int tmp_chs = nchw ? out_w : 1;
   const int nwords = (d.W + 3) >> 2;
-  const bool nchw = layout == TCB_LAYOUT_NCHW;
+  const bool fast3 = d.aligned4 && d.cin == 3 && C == 3;
+  const bool fast1 = d.aligned4 && d.cin == 1 && C == 1;
+  // vertical pass: units of 4 consecutive output elements; unit -> (line, x4) fixed per thread
   const bool vec4 = dst_aligned16 && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));
+  const int upl = nchw ? out_w / 4 : L / 4;  // units per line (vec4 only)
+  const int n_units = vec4 ? (nchw ? C * upl : upl) : 0;
   const int32_t* vg = pool + d.vg_off;
   uint8_t* dimg = dst + (size_t)img * C * out_h * out_w * elem;
   int yy_next = yy0;
+  const int my_ln = (nchw && upl > 0) ? tid / upl : 0;  // this thread's first unit, hoisted out of the row loop
+  const int my_x4 = (nchw && upl > 0) ? tid - my_ln * upl : tid;
 
-  for (int g = g_first; g <= g_last; g++) {
-    const int s = (g - g_first) % d.nst;
-    mbar_wait(&bars[s], ((g - g_first) / d.nst) & 1);
-    // ---- de-interleave stage s -> P4 ------------------------------------------------------------
-    {
-      const uint8_t* stage = raw + (size_t)s * d.stage_bytes;
-      const uint32_t lead = (uint32_t)((reinterpret_cast<uintptr_t>(d.src) + (size_t)(4 * g) * d.pitch) & 15);
-      const int nrows = min(4, d.H - 4 * g);
-      if (d.aligned4 && d.cin == 3 && C == 3) {
-        for (int w = tid; w < nwords; w += nthreads) {
-          uint32_t R[4], G[4], B[4];
+  // de-interleave of the i-th group (stage i & 1) into P4 buffer i & 1
+  auto deinterleave = [&](int i) {
+    const int g = g_first + i;
+    const uint8_t* stage = raw + (size_t)(i & 1) * d.stage_bytes;
+    const uint32_t lead = (uint32_t)((reinterpret_cast<uintptr_t>(d.src) + (size_t)(4 * g) * d.pitch) & 15);
+    const int nrows = min(4, d.H - 4 * g);
+    uint4* Pb = P4 + (size_t)(i & 1) * C * wqp;
+    const uint8_t* r0 = stage + lead;
+    if (fast3) {
+      for (int w = tid; w < nwords; w += nthreads) {
+        uint32_t R[4], G[4], B[4];
 #pragma unroll
-          for (int r = 0; r < 4; r++) {
-            uint32_t x0 = 0, x1 = 0, x2 = 0;
-            if (r < nrows) {
-              const uint32_t* rp = reinterpret_cast<const uint32_t*>(stage + lead + (size_t)r * d.pitch) + 3 * w;
-              x0 = rp[0]; x1 = rp[1]; x2 = rp[2];  // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
-            }
-            R[r] = __byte_perm(__byte_perm(x0, x1, 0x0630), x2, 0x5210);
-            G[r] = __byte_perm(__byte_perm(x0, x1, 0x0741), x2, 0x6210);
-            B[r] = __byte_perm(__byte_perm(x0, x1, 0x0052), x2, 0x7410);
+        for (int r = 0; r < 4; r++) {
+          uint32_t x0 = 0, x1 = 0, x2 = 0;
+          if (r < nrows) {
+            const uint32_t* rp = reinterpret_cast<const uint32_t*>(r0 + r * d.pitch) + 3 * w;
+            x0 = rp[0]; x1 = rp[1]; x2 = rp[2];  // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
           }
-          P4[w] = make_uint4(R[0], R[1], R[2], R[3]);
-          P4[(C > 1 ? 1 : 0) * d.wq + w] = make_uint4(G[0], G[1], G[2], G[3]);
-          P4[(C > 2 ? 2 : 0) * d.wq + w] = make_uint4(B[0], B[1], B[2], B[3]);
+          R[r] = __byte_perm(__byte_perm(x0, x1, 0x0630), x2, 0x5210);
+          G[r] = __byte_perm(__byte_perm(x0, x1, 0x0741), x2, 0x6210);
+          B[r] = __byte_perm(__byte_perm(x0, x1, 0x0052), x2, 0x7410);
         }
-      } else if (d.aligned4 && d.cin == 1 && C == 1) {
-        for (int w = tid; w < nwords; w += nthreads) {
-          uint32_t v[4];
+        const int pw = p4_phys(w);
+        Pb[pw] = make_uint4(R[0], R[1], R[2], R[3]);
+        Pb[(C > 1 ? 1 : 0) * wqp + pw] = make_uint4(G[0], G[1], G[2], G[3]);
+        Pb[(C > 2 ? 2 : 0) * wqp + pw] = make_uint4(B[0], B[1], B[2], B[3]);
+      }
+    } else if (fast1) {
+      for (int w = tid; w < nwords; w += nthreads) {
+        uint32_t v[4];
 #pragma unroll
-          for (int r = 0; r < 4; r++)
-            v[r] = r < nrows ? reinterpret_cast<const uint32_t*>(stage + lead + (size_t)r * d.pitch)[w] : 0u;
-          P4[w] = make_uint4(v[0], v[1], v[2], v[3]);
-        }
-      } else {  // any channel conversion / unaligned rows: byte-wise
-        for (int i = tid; i < nwords * C; i += nthreads) {
-          const int ch = i / nwords, w = i - ch * nwords;
-          uint32_t v[4];
+        for (int r = 0; r < 4; r++)
+          v[r] = r < nrows ? reinterpret_cast<const uint32_t*>(r0 + r * d.pitch)[w] : 0u;
+        Pb[p4_phys(w)] = make_uint4(v[0], v[1], v[2], v[3]);
+      }
+    } else {  // any channel conversion / rows not 4-byte aligned: byte-wise
+      for (int it = tid; it < nwords * C; it += nthreads) {
+        const int ch = it / nwords, w = it - ch * nwords;
+        uint32_t v[4];
 #pragma unroll
-          for (int r = 0; r < 4; r++) {
-            uint32_t word = 0;
-            if (r < nrows) {
-              const uint8_t* row = stage + lead + (size_t)r * d.pitch;
+        for (int r = 0; r < 4; r++) {
+          uint32_t word = 0;
+          if (r < nrows) {
+            const uint8_t* row = r0 + (size_t)r * d.pitch;
 #pragma unroll
-              for (int b = 0; b < 4; b++) {
-                const int x = 4 * w + b;
-                if (x < d.W) word |= fetch_conv(row, d.cin, C, x, ch) << (8 * b);
-              }
+            for (int bb = 0; bb < 4; bb++) {
+              const int x = 4 * w + bb;
+              if (x < d.W) word |= fetch_conv(row, d.cin, C, x, ch) << (8 * bb);
             }
-            v[r] = word;
           }
-          P4[ch * d.wq + w] = make_uint4(v[0], v[1], v[2], v[3]);
+          v[r] = word;
         }
+        Pb[ch * wqp + p4_phys(w)] = make_uint4(v[0], v[1], v[2], v[3]);
       }
     }
-    __syncthreads();  // P4 complete; stage s fully consumed
-    if (tid == 0 && g + d.nst <= g_last) issue(g + d.nst);
+  };
 
-    // ---- horizontal pass: 4 rows x C channels per thread ---------------------------------------
+  // vertical pass of output row yy (all groups it needs are in the ring)
+  auto vertical = [&](int yy) {
+    const int gv0 = vg[2 * yy];
+    const int32_t* vc = pool + d.vc_off + (size_t)yy * d.nwv * 3;
+    const int slot0 = (gv0 - g_first) % ng;
+    if (vec4) {
+      for (int u4 = tid; u4 < n_units; u4 += nthreads) {
+        int ln = my_ln, x4 = my_x4;
+        if (u4 != tid) {
+          ln = 0; x4 = u4;
+          if (nchw) { ln = u4 / upl; x4 = u4 - ln * upl; }
+        }
+        const int i0 = nchw ? ln * out_w + 4 * x4 : 4 * x4;  // word index inside a slot
+        uint32_t a[4][3];
+#pragma unroll
+        for (int v = 0; v < 4; v++) { a[v][0] = 0; a[v][1] = 0; a[v][2] = 0; }
+        int slot = slot0;
+        for (int j = 0; j < d.nwv; j++) {
+          const uint32_t k0 = vc[3 * j], k1 = vc[3 * j + 1], k2 = vc[3 * j + 2];
+          const uint4 px = *reinterpret_cast<const uint4*>(tmp4 + (size_t)slot * L + i0);
+          a[0][0] = __dp4a(px.x, k0, a[0][0]); a[0][1] = __dp4a(px.x, k1, a[0][1]); a[0][2] = __dp4a(px.x, k2, a[0][2]);
+          a[1][0] = __dp4a(px.y, k0, a[1][0]); a[1][1] = __dp4a(px.y, k1, a[1][1]); a[1][2] = __dp4a(px.y, k2, a[1][2]);
+          a[2][0] = __dp4a(px.z, k0, a[2][0]); a[2][1] = __dp4a(px.z, k1, a[2][1]); a[2][2] = __dp4a(px.z, k2, a[2][2]);
+          a[3][0] = __dp4a(px.w, k0, a[3][0]); a[3][1] = __dp4a(px.w, k1, a[3][1]); a[3][2] = __dp4a(px.w, k2, a[3][2]);
+          if (++slot == ng) slot = 0;
+        }
+        uint32_t u[4];
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+          const uint32_t acc = (1u << (kPrecisionBits - 1)) + a[v][0] + (a[v][1] << 8) + (a[v][2] << 16);
+          u[v] = min(acc >> kPrecisionBits, 255u);
+        }
+        size_t e0;
+        int chv[4];
+        if (nchw) {
+          e0 = ((size_t)ln * out_h + yy) * out_w + 4 * x4;
+          chv[0] = chv[1] = chv[2] = chv[3] = ln;
+        } else {
+          e0 = (size_t)yy * L + i0;
+          if (C == 3) {
+            const int c0 = x4 % 3;  // (4 * x4) % 3
+            chv[0] = c0; chv[1] = c0 == 2 ? 0 : c0 + 1; chv[2] = chv[1] == 2 ? 0 : chv[1] + 1; chv[3] = c0;
+          } else {
+            chv[0] = chv[1] = chv[2] = chv[3] = 0;
+          }
+        }
+        if (elem == 4) {
+          const uint32_t* l32 = reinterpret_cast<const uint32_t*>(lut);
+          st_global_v4(dimg + e0 * 4, __ldg(l32 + chv[0] * 256 + u[0]), __ldg(l32 + chv[1] * 256 + u[1]),
+                       __ldg(l32 + chv[2] * 256 + u[2]), __ldg(l32 + chv[3] * 256 + u[3]));
+        } else if (elem == 2) {
+          const uint16_t* l16 = reinterpret_cast<const uint16_t*>(lut);
+          const uint32_t lo = __ldg(l16 + chv[0] * 256 + u[0]) | ((uint32_t)__ldg(l16 + chv[1] * 256 + u[1]) << 16);
+          const uint32_t hi = __ldg(l16 + chv[2] * 256 + u[2]) | ((uint32_t)__ldg(l16 + chv[3] * 256 + u[3]) << 16);
+          st_global_v2(dimg + e0 * 2, lo, hi);
+        } else if (elem == 1) {
+          const uint32_t w = __ldg(lut + chv[0] * 256 + u[0]) | ((uint32_t)__ldg(lut + chv[1] * 256 + u[1]) << 8) |
+                             ((uint32_t)__ldg(lut + chv[2] * 256 + u[2]) << 16) |
+                             ((uint32_t)__ldg(lut + chv[3] * 256 + u[3]) << 24);
+          *reinterpret_cast<uint32_t*>(dimg + e0) = w;
+        } else {
+          const uint2* l64 = reinterpret_cast<const uint2*>(lut);
+          const uint2 q0 = __ldg(l64 + chv[0] * 256 + u[0]), q1 = __ldg(l64 + chv[1] * 256 + u[1]);
+          const uint2 q2 = __ldg(l64 + chv[2] * 256 + u[2]), q3 = __ldg(l64 + chv[3] * 256 + u[3]);
+          st_global_v4(dimg + e0 * 8, q0.x, q0.y, q1.x, q1.y);
+          st_global_v4(dimg + e0 * 8 + 16, q2.x, q2.y, q3.x, q3.y);
+        }
+      }
+    } else {
+      for (int i = tid; i < L; i += nthreads) {
+        uint32_t a0 = 0, a1 = 0, a2 = 0;
+        int slot = slot0;
+        for (int j = 0; j < d.nwv; j++) {
+          const uint32_t px = tmp4[(size_t)slot * L + i];
+          a0 = __dp4a(px, (uint32_t)vc[3 * j], a0); a1 = __dp4a(px, (uint32_t)vc[3 * j + 1], a1);
+          a2 = __dp4a(px, (uint32_t)vc[3 * j + 2], a2);
+          if (++slot == ng) slot = 0;
+        }
+        const uint32_t acc = (1u << (kPrecisionBits - 1)) + a0 + (a1 << 8) + (a2 << 16);
+        const uint32_t u = min(acc >> kPrecisionBits, 255u);
+        size_t e;
+        int ch;
+        if (nchw) { ch = i / out_w; e = ((size_t)ch * out_h + yy) * out_w + (i - ch * out_w); }
+        else { ch = i % C; e = (size_t)yy * L + i; }
+        const uint8_t* le = lut + ((size_t)ch * 256 + u) * elem;
+        if (elem == 4) reinterpret_cast<uint32_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint32_t*>(le));
+        else if (elem == 2) reinterpret_cast<uint16_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint16_t*>(le));
+        else if (elem == 1) dimg[e] = __ldg(le);
+        else reinterpret_cast<unsigned long long*>(dimg)[e] = __ldg(reinterpret_cast<const unsigned long long*>(le));
+      }
+    }
+  };
+
+  // ---- prologue: de-interleave the first group -----------------------------------------------------
+  mbar_wait(&bars[0], 0);
+  deinterleave(0);
+  __syncthreads();
+  if (tid == 0 && n_groups > 2) issue(2);
+
+  int slot = 0;
+  for (int i = 0; i < n_groups; i++) {
+    const int g = g_first + i;
+    // (a) de-interleave the next group into the other P4 buffer
+    if (i + 1 < n_groups) {
+      mbar_wait(&bars[(i + 1) & 1], ((i + 1) >> 1) & 1);
+      deinterleave(i + 1);
+    }
+    // (b) horizontal pass of group g: 4 rows x C channels per thread
     if (xx < out_w) {
-      uint32_t* slot = tmp4 + (size_t)(g % ng) * L;
+      const uint4* Pb = P4 + (size_t)(i & 1) * C * wqp;
+      uint32_t* out = tmp4 + (size_t)slot * L + tmp_idx0;
 #pragma unroll
       for (int ch = 0; ch < C; ch++) {
         uint32_t a[4][3];
 #pragma unroll
         for (int r = 0; r < 4; r++) { a[r][0] = 0; a[r][1] = 0; a[r][2] = 0; }
-        const uint4* p = P4 + ch * d.wq + w0;
+        const uint4* p = Pb + ch * wqp;
 #pragma unroll
         for (int j = 0; j < NW; j++) {
-          const uint4 v = p[j];
+          const uint4 v = p[poff[j]];
           a[0][0] = __dp4a(v.x, kc[j][0], a[0][0]); a[0][1] = __dp4a(v.x, kc[j][1], a[0][1]); a[0][2] = __dp4a(v.x, kc[j][2], a[0][2]);
           a[1][0] = __dp4a(v.y, kc[j][0], a[1][0]); a[1][1] = __dp4a(v.y, kc[j][1], a[1][1]); a[1][2] = __dp4a(v.y, kc[j][2], a[1][2]);
           a[2][0] = __dp4a(v.z, kc[j][0], a[2][0]); a[2][1] = __dp4a(v.z, kc[j][1], a[2][1]); a[2][2] = __dp4a(v.z, kc[j][2], a[2][2]);
           a[3][0] = __dp4a(v.w, kc[j][0], a[3][0]); a[3][1] = __dp4a(v.w, kc[j][1], a[3][1]); a[3][2] = __dp4a(v.w, kc[j][2], a[3][2]);
         }
-        uint32_t packed = 0;
+        uint32_t u[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) {
           const uint32_t acc = (1u << (kPrecisionBits - 1)) + a[r][0] + (a[r][1] << 8) + (a[r][2] << 16);
-          packed |= min(acc >> kPrecisionBits, 255u) << (8 * r);
+          u[r] = min(acc >> kPrecisionBits, 255u);
         }
-        slot[nchw ? ch * out_w + xx : xx * C + ch] = packed;
+        out[ch * tmp_chs] = __byte_perm(__byte_perm(u[0], u[1], 0x0040), __byte_perm(u[2], u[3], 0x0040), 0x5410);
       }
     }
-    __syncthreads();  // tmp4 slot visible; P4 free for the next group
-
-    // ---- vertical pass for every output row whose last group has arrived -----------------------
-    while (yy_next < yy1 && vg[2 * yy_next + 1] <= g) {
-      const int yy = yy_next;
-      const int gv0 = vg[2 * yy];
-      const int32_t* vc = pool + d.vc_off + (size_t)yy * d.nwv * 3;
-      if (vec4) {
-        for (int u4 = tid; u4 < L / 4; u4 += nthreads) {
-          const int i0 = 4 * u4;
-          uint32_t a[4][3];
-#pragma unroll
-          for (int v = 0; v < 4; v++) { a[v][0] = 0; a[v][1] = 0; a[v][2] = 0; }
-          for (int j = 0; j < d.nwv; j++) {
-            const uint32_t k0 = vc[3 * j], k1 = vc[3 * j + 1], k2 = vc[3 * j + 2];
-            const uint4 px = *reinterpret_cast<const uint4*>(tmp4 + (size_t)((gv0 + j) % ng) * L + i0);
-            a[0][0] = __dp4a(px.x, k0, a[0][0]); a[0][1] = __dp4a(px.x, k1, a[0][1]); a[0][2] = __dp4a(px.x, k2, a[0][2]);
-            a[1][0] = __dp4a(px.y, k0, a[1][0]); a[1][1] = __dp4a(px.y, k1, a[1][1]); a[1][2] = __dp4a(px.y, k2, a[1][2]);
-            a[2][0] = __dp4a(px.z, k0, a[2][0]); a[2][1] = __dp4a(px.z, k1, a[2][1]); a[2][2] = __dp4a(px.z, k2, a[2][2]);
-            a[3][0] = __dp4a(px.w, k0, a[3][0]); a[3][1] = __dp4a(px.w, k1, a[3][1]); a[3][2] = __dp4a(px.w, k2, a[3][2]);
-          }
-          uint32_t u[4];
-#pragma unroll
-          for (int v = 0; v < 4; v++) {
-            const uint32_t acc = (1u << (kPrecisionBits - 1)) + a[v][0] + (a[v][1] << 8) + (a[v][2] << 16);
-            u[v] = min(acc >> kPrecisionBits, 255u);
-          }
-          // destination element index of word i0 (4 consecutive elements share a line)
-          size_t e0;
-          int ch0, chs;
-          if (nchw) {
-            const int ch = i0 / out_w, x = i0 - ch * out_w;
-            e0 = ((size_t)ch * out_h + yy) * out_w + x; ch0 = ch; chs = 0;
-          } else {
-            e0 = (size_t)yy * L + i0; ch0 = i0 % C; chs = 1;
-          }
-          int chv[4];
-#pragma unroll
-          for (int v = 0; v < 4; v++) { int c2 = ch0 + chs * v; chv[v] = chs ? c2 % C : c2; }
-          if (elem == 4) {
-            const uint32_t* l32 = reinterpret_cast<const uint32_t*>(s_lut);
-            st_global_v4(dimg + e0 * 4, l32[chv[0] * 256 + u[0]], l32[chv[1] * 256 + u[1]],
-                         l32[chv[2] * 256 + u[2]], l32[chv[3] * 256 + u[3]]);
-          } else if (elem == 2) {
-            const uint16_t* l16 = reinterpret_cast<const uint16_t*>(s_lut);
-            const uint32_t lo = l16[chv[0] * 256 + u[0]] | ((uint32_t)l16[chv[1] * 256 + u[1]] << 16);
-            const uint32_t hi = l16[chv[2] * 256 + u[2]] | ((uint32_t)l16[chv[3] * 256 + u[3]] << 16);
-            st_global_v2(dimg + e0 * 2, lo, hi);
-          } else if (elem == 1) {
-            const uint32_t w = s_lut[chv[0] * 256 + u[0]] | ((uint32_t)s_lut[chv[1] * 256 + u[1]] << 8) |
-                               ((uint32_t)s_lut[chv[2] * 256 + u[2]] << 16) | ((uint32_t)s_lut[chv[3] * 256 + u[3]] << 24);
-            *reinterpret_cast<uint32_t*>(dimg + e0) = w;
-          } else {
-            const uint2* l64 = reinterpret_cast<const uint2*>(s_lut);
-            const uint2 q0 = l64[chv[0] * 256 + u[0]], q1 = l64[chv[1] * 256 + u[1]];
-            const uint2 q2 = l64[chv[2] * 256 + u[2]], q3 = l64[chv[3] * 256 + u[3]];
-            st_global_v4(dimg + e0 * 8, q0.x, q0.y, q1.x, q1.y);
-            st_global_v4(dimg + e0 * 8 + 16, q2.x, q2.y, q3.x, q3.y);
-          }
-        }
-      } else {
-        for (int i = tid; i < L; i += nthreads) {
-          uint32_t a0 = 0, a1 = 0, a2 = 0;
-          for (int j = 0; j < d.nwv; j++) {
-            const uint32_t px = tmp4[(size_t)((gv0 + j) % ng) * L + i];
-            a0 = __dp4a(px, (uint32_t)vc[3 * j], a0); a1 = __dp4a(px, (uint32_t)vc[3 * j + 1], a1);
-            a2 = __dp4a(px, (uint32_t)vc[3 * j + 2], a2);
-          }
-          const uint32_t acc = (1u << (kPrecisionBits - 1)) + a0 + (a1 << 8) + (a2 << 16);
-          const uint32_t u = min(acc >> kPrecisionBits, 255u);
-          size_t e;
-          int ch;
-          if (nchw) { ch = i / out_w; e = ((size_t)ch * out_h + yy) * out_w + (i - ch * out_w); }
-          else { ch = i % C; e = (size_t)yy * L + i; }
-          const uint8_t* le = s_lut + ((size_t)ch * 256 + u) * elem;
-          if (elem == 4) reinterpret_cast<uint32_t*>(dimg)[e] = *reinterpret_cast<const uint32_t*>(le);
-          else if (elem == 2) reinterpret_cast<uint16_t*>(dimg)[e] = *reinterpret_cast<const uint16_t*>(le);
-          else if (elem == 1) dimg[e] = *le;
-          else reinterpret_cast<uint64_t*>(dimg)[e] = *reinterpret_cast<const uint64_t*>(le);
-        }
-      }
-      yy_next++;
-    }
-    // the next iteration's de-interleave only touches P4/raw; its __syncthreads orders this
-    // vertical pass before the next horizontal pass overwrites a tmp4 slot
+    // (c) vertical pass of the rows whose last group was written in the previous phase
+    while (yy_next < yy1 && vg[2 * yy_next + 1] < g) vertical(yy_next++);
+    __syncthreads();
+    if (tid == 0 && i + 3 < n_groups) issue(i + 3);  // stage (i+1)&1 was drained in (a)
+    if (++slot == ng) slot = 0;
   }
+  while (yy_next < yy1) vertical(yy_next++);
 }
 
 // ---- host side ---------------------------------------------------------------------------------------
@@ -384,6 +451,7 @@ struct FusedGeom {
 };
 
 static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc& d, FusedGeom* g) {
+  (void)elem;
   if (d.p1_axis != AXIS_H || d.p2_axis != AXIS_V) return false;
   if (!((d.cin == 3 && c == 3) || (d.cin == 1 && c == 1) || (d.cin == 4 && c == 3) ||
         ((d.cin == 3 || d.cin == 4) && c == 1)))
@@ -398,17 +466,11 @@ static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc&
   const int nwv = pack_axis(b, k, ksv, out_h, 0, packed, first);
   if (nwv > 24) return false;
   g->nw_class = cls; g->nwv = nwv;
-  g->wq = ((d.W + 3) >> 2) + cls + 1;
+  g->wq = p4_phys(((d.W + 3) >> 2) + cls + 1) + 1;  // physical granules per plane
   g->stage_bytes = (int)round_up((uint64_t)4 * d.pitch + 48, 128);
-  g->threads = std::max(128, (int)round_up(out_w, 32));
-  const size_t fixed = 64 + round_up((uint64_t)c * 256 * elem, 128) + (size_t)c * g->wq * 16 +
-                       (size_t)(nwv + 1) * out_w * c * 4 + 128;
-  g->nst = 3;
-  g->smem = fixed + (size_t)g->nst * g->stage_bytes;
-  if (g->smem > 110 * 1024) {  // prefer two resident CTAs per SM over a third stage
-    g->nst = 2;
-    g->smem = fixed + (size_t)g->nst * g->stage_bytes;
-  }
+  g->threads = out_w > 256 ? 512 : 256;
+  g->nst = 2;
+  g->smem = 64 + (size_t)2 * g->stage_bytes + (size_t)2 * c * g->wq * 16 + (size_t)(nwv + 1) * out_w * c * 4 + 64;
   return g->smem <= kFusedMaxSmem;
 }
 
@@ -450,15 +512,20 @@ static int launch_class(const Plan& p, const FusedPlan& fp, int cls, void* dst, 
   const int threads = fp.threads.at(cls);
   const int32_t* work = fp.d_work + fp.work_off.at(cls);
   const int al = (reinterpret_cast<uintptr_t>(dst) % 16 == 0) ? 1 : 0;
-  if (p.c == 3) {
-    TCB_CUDA(cudaFuncSetAttribute(k_preprocess_fused<NW, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_preprocess_fused<NW, 3><<<ctas, threads, smem, s>>>(fp.d_desc, work, fp.d_pool, p.d_lut, (uint8_t*)dst, p.out_h,
-                                                          p.out_w, p.layout, p.elem, al);
+#define TCB_FUSED(CC, BG)                                                                                 \
+  do {                                                                                                    \
+    TCB_CUDA(cudaFuncSetAttribute(k_preprocess_fused<NW, CC, BG>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                  (int)smem));                                                            \
+    k_preprocess_fused<NW, CC, BG><<<ctas, threads, smem, s>>>(fp.d_desc, work, fp.d_pool, p.d_lut,       \
+                                                               (uint8_t*)dst, p.out_h, p.out_w, p.layout, \
+                                                               p.elem, al);                               \
+  } while (0)
+  if (threads > 256) {
+    if (p.c == 3) TCB_FUSED(3, true); else TCB_FUSED(1, true);
   } else {
-    TCB_CUDA(cudaFuncSetAttribute(k_preprocess_fused<NW, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_preprocess_fused<NW, 1><<<ctas, threads, smem, s>>>(fp.d_desc, work, fp.d_pool, p.d_lut, (uint8_t*)dst, p.out_h,
-                                                          p.out_w, p.layout, p.elem, al);
+    if (p.c == 3) TCB_FUSED(3, false); else TCB_FUSED(1, false);
   }
+#undef TCB_FUSED
   count_launch();
   return TCB_OK;
 }
