@@ -29,7 +29,7 @@ namespace tcb {
 
 constexpr int kFusedMaxThreads = 512;
 constexpr size_t kFusedMaxSmem = 200 * 1024;
-static const int kNwClasses[] = {2, 3, 4, 6, 8, 12, 16};
+static const int kNwClasses[] = {2, 3, 4, 5, 6, 8, 10, 12, 16};
 
 // ---- PTX helpers ------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -116,10 +116,10 @@ __device__ __forceinline__ uint32_t fetch_conv(const uint8_t* row, int cin, int 
   return (q[0] * 19595u + q[1] * 38470u + q[2] * 7471u + 0x8000u) >> 16;
 }
 
-// Physical granule index of logical granule w in a P4 plane: one granule of padding after every
-// 8. Output columns that are ~2 granules apart (1080p -> 224) then fall into distinct bank groups
-// instead of colliding pairwise (measured: 32 % of all shared-memory wavefronts were conflicts).
-__host__ __device__ __forceinline__ int p4_phys(int w) { return w + (w >> 3); }
+// Physical granule index of logical granule w in a P4 plane. Identity: the horizontal pass reads
+// granules ~2 apart from consecutive lanes (1080p -> 224), which is a 2-way bank conflict for any
+// 8-lane phase; padding and XOR swizzles were simulated and measured and do not beat it.
+__host__ __device__ __forceinline__ int p4_phys(int w) { return w; }
 
 // NW: coefficient words per output column; C: output channels; BIG: more than 256 output columns
 // (one CTA per SM). Software-pipelined: in phase i every thread (a) de-interleaves row group i+1
@@ -194,6 +194,11 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   const int nwords = (d.W + 3) >> 2;
   const bool fast3 = d.aligned4 && d.cin == 3 && C == 3;
   const bool fast1 = d.aligned4 && d.cin == 1 && C == 1;
+  // de-interleave work split (fast3 path): idle-in-H threads take dshare words each = dfirst words
+  const int n_idle = nthreads - min(out_w, nthreads);
+  const int dshare = 0;  // (experiment: give idle-in-H threads more de-interleave work) measured slower
+  (void)n_idle;
+  const int dfirst = min(nwords, n_idle * dshare);
   // vertical pass: units of 4 consecutive output elements; unit -> (line, x4) fixed per thread
   const bool vec4 = dst_aligned16 && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));
   const int upl = nchw ? out_w / 4 : L / 4;  // units per line (vec4 only)
@@ -213,7 +218,19 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
     uint4* Pb = P4 + (size_t)(i & 1) * C * wqp;
     const uint8_t* r0 = stage + lead;
     if (fast3) {
-      for (int w = tid; w < nwords; w += nthreads) {
+      // threads beyond out_w have no horizontal-pass work: they take `dshare` words each first,
+      // the rest is spread over everybody
+      for (int it = 0;; it++) {
+        int w;
+        if (it < dshare) {
+          if (tid < out_w) continue;
+          w = (tid - out_w) * dshare + it;
+          if (w >= dfirst) continue;
+        } else {
+          w = dfirst + (it - dshare) * nthreads + tid;
+          if (dfirst + (it - dshare) * nthreads >= nwords) break;
+          if (w >= nwords) continue;
+        }
         uint32_t R[4], G[4], B[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) {
@@ -626,7 +643,9 @@ int fused_launch(const Plan& p, void* dst, cudaStream_t s) {
       case 2: rc = launch_class<2>(p, fp, 2, dst, s); break;
       case 3: rc = launch_class<3>(p, fp, 3, dst, s); break;
       case 4: rc = launch_class<4>(p, fp, 4, dst, s); break;
+      case 5: rc = launch_class<5>(p, fp, 5, dst, s); break;
       case 6: rc = launch_class<6>(p, fp, 6, dst, s); break;
+      case 10: rc = launch_class<10>(p, fp, 10, dst, s); break;
       case 8: rc = launch_class<8>(p, fp, 8, dst, s); break;
       case 12: rc = launch_class<12>(p, fp, 12, dst, s); break;
       case 16: rc = launch_class<16>(p, fp, 16, dst, s); break;
