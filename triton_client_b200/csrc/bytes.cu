@@ -104,80 +104,144 @@ __device__ unsigned long long lookback_exclusive(unsigned long long* status, uns
 //   s_off[e]  : blob offset of tile element e relative to the tile's first element (e in 0..nE)
 //   blob0     : global blob offset of the tile's first element
 //   e0        : global index of the tile's first element
-// Output-centric: 16 aligned output bytes per thread per step, vector store for full chunks.
+//   s_tab     : kTabSize entries of scratch (element containing every 2^tsh-th output byte)
+// Output-centric, 16 aligned output bytes at a time, in two divergence-free phases:
+//   A. interior chunks (entirely inside one payload): element found through s_tab + a short walk,
+//      4 aligned word loads (payload moves by a multiple of 4 bytes), one 128-bit store;
+//   B. boundary chunks (contain a length prefix / an element boundary / a tile edge): each is owned
+//      by exactly one element-thread, which assembles it byte-wise; all lanes of a warp are busy
+//      with boundary chunks at the same time instead of dragging the slow path through phase A.
+constexpr int kTabSize = 1024;
+
+template <bool TO_STREAM>
+__device__ __forceinline__ unsigned long long elem_start(const unsigned long long* s_off, int e) {
+  return TO_STREAM ? s_off[e] + 4ull * (unsigned)e : s_off[e];  // relative to the tile's output start
+}
+
+template <bool TO_STREAM, bool WORD_OK>
+__device__ __forceinline__ void assemble_chunk(const unsigned long long* s_off, int nE, unsigned long long A,
+                                               unsigned long long lim, unsigned long long e0, int e,
+                                               unsigned long long q, unsigned long long mis,
+                                               const uint8_t* __restrict__ src, uint8_t* __restrict__ vd) {
+  const unsigned long long cb = q << 4;
+  const unsigned long long a = max(cb, A), b = min(cb + 16, lim);
+  if (a >= b) return;
+  // e: an element at or before the one holding byte a; walk forward as needed
+  unsigned long long es = A + elem_start<TO_STREAM>(s_off, e);
+  unsigned long long ee = A + elem_start<TO_STREAM>(s_off, e + 1);
+  uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int bi = 0; bi < 16; bi++) {
+    const unsigned long long p = cb + bi;
+    if (p < a || p >= b) continue;
+    while (ee <= p && e + 1 < nE) {
+      e++;
+      es = ee;
+      ee = A + elem_start<TO_STREAM>(s_off, e + 1);
+    }
+    uint32_t byte;
+    if (TO_STREAM && p < es + 4) {
+      const unsigned long long len = s_off[e + 1] - s_off[e];
+      byte = (uint32_t)(len >> (8 * (p - es))) & 0xffu;
+    } else {
+      const unsigned long long E1 = 4ull * (e0 + e + 1);
+      byte = src[TO_STREAM ? p - mis - E1 : p - mis + E1];
+    }
+    w[bi >> 2] |= byte << (8 * (bi & 3));
+  }
+  if (a == cb && b == cb + 16) {
+    st_v4(vd + cb, w[0], w[1], w[2], w[3]);
+  } else {
+    for (unsigned long long p = a; p < b; p++) vd[p] = (uint8_t)(w[(p - cb) >> 2] >> (8 * (p & 3)));
+  }
+}
+
 template <bool TO_STREAM, bool WORD_OK>
 __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int nE,
                                           unsigned long long blob0, unsigned long long e0,
                                           const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
-                                          unsigned long long dst_capacity) {
+                                          unsigned long long dst_capacity, unsigned short* s_tab) {
   // output coordinates are shifted by `mis` so that multiples of 16 are 16-byte aligned addresses
   const unsigned long long mis = reinterpret_cast<uintptr_t>(dst) & 15;
   uint8_t* vd = dst - mis;
-  // tile output range [o0, o1) in unshifted output offsets
   const unsigned long long o0 = TO_STREAM ? blob0 + 4 * e0 : blob0;
-  const unsigned long long o1 = TO_STREAM ? blob0 + s_off[nE] + 4 * (e0 + nE) : blob0 + s_off[nE];
+  const unsigned long long total = elem_start<TO_STREAM>(s_off, nE);  // tile output bytes
+  const unsigned long long o1 = o0 + total;
   const unsigned long long lim = min(o1, dst_capacity) + mis;
   const unsigned long long A = o0 + mis;
   if (lim <= A) return;
-  const unsigned long long q0 = A >> 4, q1 = (lim + 15) >> 4;
+  // ---- lookup table: s_tab[t] = element containing output byte (t << tsh) of the tile ------------
+  int tsh = 8;
+  while ((total >> tsh) >= (unsigned long long)kTabSize) tsh++;
+  for (int e = threadIdx.x; e < nE; e += blockDim.x) {
+    const unsigned long long s0 = elem_start<TO_STREAM>(s_off, e), s1 = elem_start<TO_STREAM>(s_off, e + 1);
+    if (s1 > s0) {
+      const unsigned long long t0 = (s0 + (1ull << tsh) - 1) >> tsh, t1 = (s1 - 1) >> tsh;
+      for (unsigned long long t = t0; t <= t1; t++) s_tab[t] = (unsigned short)e;
+    }
+  }
+  __syncthreads();
+  // ---- phase A: interior chunks ----------------------------------------------------------------------
+  const unsigned long long q0 = (A + 15) >> 4, q1 = lim >> 4;  // chunks fully inside [A, lim)
   for (unsigned long long q = q0 + threadIdx.x; q < q1; q += blockDim.x) {
     const unsigned long long cb = q << 4;
-    const unsigned long long a = max(cb, A), b = min(cb + 16, lim);
-    // element containing output byte a: largest e with start(e) <= a
-    const unsigned long long rel = a - A;
-    int lo = 0, hi = nE;
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      const unsigned long long st = TO_STREAM ? s_off[mid] + 4ull * mid : s_off[mid];
-      if (st <= rel) lo = mid; else hi = mid;
+    const unsigned long long rel = cb - A;
+    int e = s_tab[rel >> tsh];
+    unsigned long long nx = elem_start<TO_STREAM>(s_off, e + 1);
+    while (nx <= rel) {  // short walk inside one table block
+      e++;
+      nx = elem_start<TO_STREAM>(s_off, e + 1);
     }
-    int e = lo;
-    // element bounds in shifted output coordinates
-    unsigned long long es, ps, ee;  // element start (header if TO_STREAM), payload start, end
-    auto bounds = [&](int el) {
-      if (TO_STREAM) {
-        es = A + s_off[el] + 4ull * el; ps = es + 4; ee = A + s_off[el + 1] + 4ull * (el + 1);
-      } else {
-        es = A + s_off[el]; ps = es; ee = A + s_off[el + 1];
-      }
-    };
-    bounds(e);
-    uint32_t w[4];
-#pragma unroll
-    for (int wi = 0; wi < 4; wi++) {
-      const unsigned long long wa = cb + 4 * wi;
-      w[wi] = 0;
-      if (wa >= b || wa + 4 <= a) continue;
-      while (ee <= wa && e + 1 < nE) { e++; bounds(e); }
-      // source offset of output byte p inside element el: TO_STREAM: blob[p - mis - 4*(E+1)],
-      // else stream[p - mis + 4*(E+1)], E = e0 + el
-      if (WORD_OK && wa >= ps && wa + 4 <= ee && wa >= a && wa + 4 <= b) {
-        const unsigned long long E1 = 4ull * (e0 + e + 1);
-        w[wi] = ldg_u32(src + (TO_STREAM ? wa - mis - E1 : wa - mis + E1));
-      } else {
-        uint32_t v = 0;
-#pragma unroll
-        for (int bi = 0; bi < 4; bi++) {
-          const unsigned long long p = wa + bi;
-          if (p < a || p >= b) continue;
-          while (ee <= p && e + 1 < nE) { e++; bounds(e); }
-          uint32_t byte;
-          if (TO_STREAM && p < ps) {
-            const unsigned long long len = s_off[e + 1] - s_off[e];
-            byte = (uint32_t)(len >> (8 * (p - es))) & 0xffu;
-          } else {
-            const unsigned long long E1 = 4ull * (e0 + e + 1);
-            byte = src[TO_STREAM ? p - mis - E1 : p - mis + E1];
-          }
-          v |= byte << (8 * bi);
-        }
-        w[wi] = v;
-      }
-    }
-    if (a == cb && b == cb + 16) {
-      st_v4(vd + cb, w[0], w[1], w[2], w[3]);
+    const unsigned long long st = elem_start<TO_STREAM>(s_off, e);
+    if (rel + 16 > nx || (TO_STREAM && rel < st + 4)) continue;  // not interior: phase B
+    const unsigned long long E1 = 4ull * (e0 + e + 1);
+    const uint8_t* sp = src + (TO_STREAM ? cb - mis - E1 : cb - mis + E1);
+    uint32_t w0, w1, w2, w3;
+    if (WORD_OK) {
+      w0 = ldg_u32(sp); w1 = ldg_u32(sp + 4); w2 = ldg_u32(sp + 8); w3 = ldg_u32(sp + 12);
     } else {
-      for (unsigned long long p = a; p < b; p++) vd[p] = (uint8_t)(w[(p - cb) >> 2] >> (8 * (p & 3)));
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++)
+        w[k] = (uint32_t)sp[4 * k] | ((uint32_t)sp[4 * k + 1] << 8) | ((uint32_t)sp[4 * k + 2] << 16) |
+               ((uint32_t)sp[4 * k + 3] << 24);
+      w0 = w[0]; w1 = w[1]; w2 = w[2]; w3 = w[3];
+    }
+    st_v4(vd + cb, w0, w1, w2, w3);
+  }
+  // ---- phase B: boundary chunks, one owner thread each ------------------------------------------------
+  // Boundary points b_e: for TO_STREAM the prefix bytes [hs_e, hs_e + 4) of every element; otherwise
+  // the element start offsets. Chunk q is owned by the first element whose boundary touches it; the
+  // tile's head (A) and tail (lim) are the boundaries of pseudo-elements 0 and nE.
+  for (int e = threadIdx.x; e <= nE; e += blockDim.x) {
+    if (TO_STREAM) {
+      if (e < nE) {
+        const unsigned long long hs = A + elem_start<true>(s_off, e);
+        const unsigned long long qa = hs >> 4, qb = (hs + 3) >> 4;
+        bool own_a = true;
+        if (e > 0) {
+          const unsigned long long hp = A + elem_start<true>(s_off, e - 1);
+          own_a = ((hp + 3) >> 4) != qa;  // the previous prefix does not reach into qa
+        }
+        if (own_a) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, qa, mis, src, vd);
+        if (qb != qa) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e, qb, mis, src, vd);
+      } else if (lim & 15) {  // partial tail chunk with no prefix of this tile in it
+        const unsigned long long qt = lim >> 4;
+        const unsigned long long hl = A + elem_start<true>(s_off, nE - 1);
+        if (((hl + 3) >> 4) < qt) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, nE - 1, qt, mis, src, vd);
+      }
+    } else {
+      // boundary point of pseudo-element e: its start (e < nE) or the tile end (e == nE)
+      const unsigned long long be = e < nE ? A + s_off[e] : lim;
+      if ((be & 15) == 0 || be > lim) continue;  // chunk-aligned boundaries create no boundary chunk
+      const unsigned long long q = be >> 4;
+      bool own = true;
+      if (e > 0) {
+        const unsigned long long bp = A + s_off[e - 1];
+        own = (bp >> 4) < q || (bp & 15) == 0;  // previous boundary is not strictly inside chunk q
+        if ((bp >> 4) == q && (bp & 15) == 0) own = true;
+      }
+      if (own) assemble_chunk<false, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, q, mis, src, vd);
     }
   }
 }
@@ -194,6 +258,7 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
   __shared__ unsigned long long s_warp[kSerThreads / 32];
   __shared__ unsigned long long s_prefix;
   __shared__ unsigned int s_tile;
+  __shared__ unsigned short s_tab[kTabSize + 1];
   unsigned long long* status = ws + WS_HEADER_WORDS;
   if (threadIdx.x == 0) s_tile = atomicAdd(reinterpret_cast<unsigned int*>(&ws[WS_TICKET]), 1u);
   __syncthreads();
@@ -275,7 +340,7 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
                             : payload[(e0 + lo) * (unsigned long long)width + (rel - es - 4)];
     }
   } else {
-    move_tile<true, WORD_OK>(s_off, nE, blob0, e0, payload, dst, dst_capacity);
+    move_tile<true, WORD_OK>(s_off, nE, blob0, e0, payload, dst, dst_capacity, s_tab);
   }
 }
 
@@ -400,75 +465,103 @@ __device__ __forceinline__ bool chase_global(const uint8_t* __restrict__ stream,
   return true;
 }
 
-// Single CTA: verify entry[k] == exit[k-1], scan counts, decide the outcome.
-__global__ void __launch_bounds__(1024)
-k_des_resolve(unsigned long long S, unsigned long long K, long long max_elements, DesArrays A,
-              unsigned long long* hdr) {
-  __shared__ unsigned long long s_part[1024];
-  __shared__ unsigned long long s_first, s_ferr;
-  const int t = threadIdx.x;
-  const unsigned long long per = (K + 1023) / 1024;
-  const unsigned long long k0 = min((unsigned long long)t * per, K), k1 = min(k0 + per, K);
-  if (t == 0) { s_first = K; s_ferr = K; }
+// Resolve = three small kernels (the chunk count reaches 262 144 for a 2 GB stream, too many for
+// one CTA): verify entry[k] == exit[k-1] and find the first truncated chunk; look-back scan of the
+// per-chunk counts over the verified prefix; decide the outcome.
+constexpr int kResThreads = 256;
+constexpr int kResItems = 8;
+constexpr int kResTile = kResThreads * kResItems;
+enum : int { DW_FIRST = 3, DW_FERR = 6, DW_TOTAL = 7 };  // header words (DW_FIRST == DW_FIRST_MISMATCH)
+
+__global__ void __launch_bounds__(kResThreads)
+k_des_verify(unsigned long long K, DesArrays A, unsigned long long* hdr) {
+  const unsigned long long k = (unsigned long long)blockIdx.x * kResThreads + threadIdx.x;
+  if (k >= K) return;
+  const unsigned long long expect = k == 0 ? 0 : A.x[k - 1];
+  if (A.g[k] != expect) atomicMin(&hdr[DW_FIRST], k);   // hdr[DW_FIRST] starts at ~0
+  if (A.err[k]) atomicMin(&hdr[DW_FERR], k);
+}
+
+// base[k] = number of elements in verified chunks before k (chunks >= first contribute nothing)
+__global__ void __launch_bounds__(kResThreads)
+k_des_scan(unsigned long long K, DesArrays A, unsigned long long* hdr, unsigned long long* sws) {
+  __shared__ unsigned long long s_warp[kResThreads / 32];
+  __shared__ unsigned long long s_prefix;
+  __shared__ unsigned int s_tile;
+  if (threadIdx.x == 0) s_tile = atomicAdd(reinterpret_cast<unsigned int*>(&sws[WS_TICKET]), 1u);
   __syncthreads();
-  // first chunk whose entry does not continue its predecessor's chain
-  unsigned long long first = K;
-  for (unsigned long long k = k0; k < k1; k++) {
-    const unsigned long long expect = k == 0 ? 0 : A.x[k - 1];
-    if (A.g[k] != expect) { first = k; break; }
+  const unsigned int tile = s_tile;
+  const unsigned long long first = min(hdr[DW_FIRST], K);
+  const unsigned long long k0 = (unsigned long long)tile * kResTile + (unsigned long long)threadIdx.x * kResItems;
+  unsigned int c[kResItems];
+  unsigned long long tsum = 0;
+#pragma unroll
+  for (int i = 0; i < kResItems; i++) {
+    const unsigned long long k = k0 + i;
+    c[i] = (k < K && k < first) ? A.cnt[k] : 0u;
+    tsum += c[i];
   }
-  if (first < K) atomicMin(&s_first, first);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned long long incl = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
   __syncthreads();
-  first = s_first;
-  // exclusive scan of counts over the verified prefix [0, first); first truncated chunk in it
-  unsigned long long sum = 0, ferr = K;
-  for (unsigned long long k = k0; k < k1 && k < first; k++) {
-    sum += A.cnt[k];
-    if (ferr == K && A.err[k]) ferr = k;
+  unsigned long long wbase = 0, tile_total = 0;
+#pragma unroll
+  for (int w = 0; w < kResThreads / 32; w++) {
+    if (w < warp) wbase += s_warp[w];
+    tile_total += s_warp[w];
   }
-  if (ferr < K) atomicMin(&s_ferr, ferr);
-  s_part[t] = sum;
-  __syncthreads();
-  for (int o = 1; o < 1024; o <<= 1) {
-    const unsigned long long v = t >= o ? s_part[t - o] : 0;
-    __syncthreads();
-    s_part[t] += v;
-    __syncthreads();
-  }
-  unsigned long long run = s_part[t] - sum;
-  for (unsigned long long k = k0; k < k1; k++) {
-    A.base[k] = run;
-    run += (k < first) ? A.cnt[k] : 0;
+  if (warp == 0) {
+    const unsigned long long ex = lookback_exclusive(sws + WS_HEADER_WORDS, tile, tile_total, sws);
+    if (lane == 0) s_prefix = ex;
   }
   __syncthreads();
-  if (t == 0) {
-    const unsigned long long total = s_part[1023];  // elements in the verified prefix
-    ferr = s_ferr;
-    unsigned long long status, nelem, kend;
-    const bool limited = max_elements >= 0;
-    const unsigned long long M = limited ? (unsigned long long)max_elements : ~0ull;
-    // elements that decode before anything goes wrong inside the verified prefix
-    const unsigned long long good = ferr < K ? A.base[ferr] + A.cnt[ferr] : total;
-    if (limited && good >= M) {
-      unsigned long long lo = 0, hi = first;  // smallest kk with base[kk] + cnt[kk] >= M
-      while (lo < hi) {
-        const unsigned long long mid = (lo + hi) >> 1;
-        if (A.base[mid] + A.cnt[mid] >= M) hi = mid; else lo = mid + 1;
-      }
-      status = 0; nelem = M; kend = M == 0 ? 0 : lo + 1;
-    } else if (ferr < K) {
-      status = 2; nelem = good; kend = ferr + 1;  // the true chain runs off the buffer
-    } else if (first < K) {
-      status = 1; nelem = total; kend = first;    // a guessed entry was wrong: sweep
-    } else {
-      status = 0; nelem = total; kend = K;
-      const unsigned long long end = K ? A.x[K - 1] : 0;
-      if (end != S) status = 2;
-      if (limited) status = 2;  // fewer than M elements before the end: the reference unpacks past it
+  unsigned long long run = s_prefix + wbase + incl - tsum;
+#pragma unroll
+  for (int i = 0; i < kResItems; i++) {
+    const unsigned long long k = k0 + i;
+    if (k < K) A.base[k] = run;
+    run += c[i];
+  }
+  if (k0 <= K - 1 && K - 1 < k0 + kResItems) hdr[DW_TOTAL] = run;  // the thread that owns the last chunk
+}
+
+__global__ void k_des_finalize(unsigned long long S, unsigned long long K, long long max_elements,
+                               DesArrays A, unsigned long long* hdr) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const unsigned long long first = min(hdr[DW_FIRST], K);
+  const unsigned long long total = hdr[DW_TOTAL];  // elements in the verified prefix [0, first)
+  unsigned long long ferr = hdr[DW_FERR];
+  if (ferr >= first) ferr = K;                     // only errors inside the verified prefix count
+  unsigned long long status, nelem, kend;
+  const bool limited = max_elements >= 0;
+  const unsigned long long M = limited ? (unsigned long long)max_elements : ~0ull;
+  // elements that decode before anything goes wrong inside the verified prefix
+  const unsigned long long good = ferr < K ? A.base[ferr] + A.cnt[ferr] : total;
+  if (limited && good >= M) {
+    unsigned long long lo = 0, hi = first;  // smallest kk with base[kk] + cnt[kk] >= M
+    while (lo < hi) {
+      const unsigned long long mid = (lo + hi) >> 1;
+      if (A.base[mid] + A.cnt[mid] >= M) hi = mid; else lo = mid + 1;
     }
-    hdr[DW_STATUS] = status; hdr[DW_NELEM] = nelem; hdr[DW_KEND] = kend;
-    hdr[DW_FIRST_MISMATCH] = first;
+    status = 0; nelem = M; kend = M == 0 ? 0 : lo + 1;
+  } else if (ferr < K) {
+    status = 2; nelem = good; kend = ferr + 1;  // the true chain runs off the buffer
+  } else if (first < K) {
+    status = 1; nelem = total; kend = first;    // a guessed entry was wrong: sweep
+  } else {
+    status = 0; nelem = total; kend = K;
+    const unsigned long long end = K ? A.x[K - 1] : 0;
+    if (end != S) status = 2;
+    if (limited) status = 2;  // fewer than M elements before the end: the reference unpacks past it
   }
+  hdr[DW_STATUS] = status; hdr[DW_NELEM] = nelem; hdr[DW_KEND] = kend;
+  hdr[DW_FIRST_MISMATCH] = first;
 }
 
 // Sequential repair from the first mismatching chunk: re-chase chunks whose guessed entry was
@@ -561,6 +654,7 @@ k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ o
              const unsigned long long* __restrict__ hdr, uint8_t* __restrict__ blob,
              unsigned long long blob_capacity) {
   __shared__ unsigned long long s_off[kGatTile + 1];
+  __shared__ unsigned short s_tab[kTabSize + 1];
   const unsigned long long N = hdr[DW_NELEM];
   if (hdr[DW_STATUS] != 0) return;
   const unsigned long long e0 = (unsigned long long)blockIdx.x * kGatTile;
@@ -570,7 +664,7 @@ k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ o
   for (int i = threadIdx.x; i <= nE; i += kGatThreads)
     s_off[i] = (unsigned long long)offsets[e0 + i] - b0;
   __syncthreads();
-  move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity);
+  move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity, s_tab);
 }
 
 static uint64_t des_chunks(uint64_t stream_bytes) { return (stream_bytes + kDesChunk - 1) / kDesChunk; }
@@ -588,9 +682,9 @@ uint64_t TcbBytesSerializeWorkspace(uint64_t n_elements) {
 
 uint64_t TcbBytesDeserializeWorkspace(uint64_t stream_bytes) {
   const uint64_t K = des_chunks(stream_bytes) + 1;
-  // header + g, x, base (u64) + cnt, err (u32) + list (u16 * cap), each 256-byte aligned
-  return 256 + 3 * round_up(K * 8, 256) + 2 * round_up(K * 4, 256) +
-         round_up(K * kDesListCap * 2, 256);
+  // header + scan status + g, x, base (u64) + cnt, err (u32) + list (u16 * cap), each 256-byte aligned
+  return 256 + round_up((WS_HEADER_WORDS + K / kResTile + 2) * 8, 256) + 3 * round_up(K * 8, 256) +
+         2 * round_up(K * 4, 256) + round_up(K * kDesListCap * 2, 256);
 }
 
 static int serialize_common(int device_id, const void* payload_dev, const void* lengths_dev,
@@ -692,8 +786,10 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
   uint8_t* w = static_cast<uint8_t*>(workspace_dev);
   unsigned long long* hdr = reinterpret_cast<unsigned long long*>(w);
   DesArrays A;
-  uint8_t* p = w + 256;
   const uint64_t K1 = K + 1;
+  unsigned long long* sws = reinterpret_cast<unsigned long long*>(w + 256);  // scan workspace
+  const uint64_t sws_bytes = round_up((WS_HEADER_WORDS + K1 / kResTile + 2) * 8, 256);
+  uint8_t* p = w + 256 + sws_bytes;
   A.g = reinterpret_cast<unsigned long long*>(p); p += round_up(K1 * 8, 256);
   A.x = reinterpret_cast<unsigned long long*>(p); p += round_up(K1 * 8, 256);
   A.base = reinterpret_cast<unsigned long long*>(p); p += round_up(K1 * 8, 256);
@@ -703,15 +799,26 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
   const uint8_t* st = static_cast<const uint8_t*>(stream_dev);
   TCB_CUDA(cudaMemsetAsync(hdr, 0, 256, s));
   k_des_speculate<<<(unsigned)K, kDesThreads, 0, s>>>(st, stream_bytes, K, A);
-  k_des_resolve<<<1, 1024, 0, s>>>(stream_bytes, K, max_elements, A, hdr);
-  count_launch(2);
+  auto resolve = [&]() -> cudaError_t {
+    // first mismatch / first error start at ~0 (atomicMin), the scan workspace at 0
+    cudaMemsetAsync(hdr + DW_FIRST, 0xFF, 8, s);
+    cudaMemsetAsync(hdr + DW_FERR, 0xFF, 8, s);
+    cudaMemsetAsync(sws, 0, sws_bytes, s);
+    k_des_verify<<<(unsigned)((K + kResThreads - 1) / kResThreads), kResThreads, 0, s>>>(K, A, hdr);
+    k_des_scan<<<(unsigned)((K + kResTile - 1) / kResTile), kResThreads, 0, s>>>(K, A, hdr, sws);
+    k_des_finalize<<<1, 32, 0, s>>>(stream_bytes, K, max_elements, A, hdr);
+    count_launch(3);
+    return cudaGetLastError();
+  };
+  TCB_CUDA(resolve());
+  count_launch(1);
   unsigned long long h[DW_HEADER_WORDS];
   TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
   TCB_CUDA(cudaStreamSynchronize(s));
   if (h[DW_STATUS] == 1) {  // a guess was wrong: repair sequentially, then resolve again
     k_des_sweep<<<1, 32, 0, s>>>(st, stream_bytes, K, max_elements, A, hdr);
-    k_des_resolve<<<1, 1024, 0, s>>>(stream_bytes, K, max_elements, A, hdr);
-    count_launch(2);
+    TCB_CUDA(resolve());
+    count_launch(1);
     TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
     TCB_CUDA(cudaStreamSynchronize(s));
   }
