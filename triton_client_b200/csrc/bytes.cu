@@ -118,6 +118,67 @@ __device__ __forceinline__ unsigned long long elem_start(const unsigned long lon
   return TO_STREAM ? s_off[e] + 4ull * (unsigned)e : s_off[e];  // relative to the tile's output start
 }
 
+__device__ __forceinline__ uint32_t bytemask(int n) {  // low n bytes set, n clamped to [0, 4]
+  return n <= 0 ? 0u : (n >= 4 ? 0xffffffffu : ((1u << (8 * n)) - 1u));
+}
+__device__ __forceinline__ uint32_t shl_bytes(uint32_t x, int n) { return n >= 4 ? 0u : x << (8 * n); }
+__device__ __forceinline__ uint32_t shr_bytes(uint32_t x, int n) { return n >= 4 ? 0u : x >> (8 * n); }
+__device__ __forceinline__ int clamp_u64_to(unsigned long long v, int hi) {
+  return v > (unsigned long long)hi ? hi : (int)v;
+}
+// Word whose lanes selected by `mask` are needed. Aligned case: one 32-bit load (never crosses a
+// page). Misaligned case: only the needed bytes are touched.
+__device__ __forceinline__ uint32_t load_word(const uint8_t* p, bool word_ok, uint32_t mask = 0xffffffffu) {
+  if (word_ok) return ldg_u32(p);
+  uint32_t v = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+    if (mask & (0xffu << (8 * i))) v |= (uint32_t)p[i] << (8 * i);
+  return v;
+}
+
+// One aligned 32-bit word of the tile's output at tile-relative offset `rel` (rel % 4 == 0 in
+// absolute terms), composed arithmetically instead of byte by byte. `e` must be the element that
+// holds byte `rel` and is advanced by the caller. `sp` points at the source byte that corresponds
+// to output byte `rel` for an element with global index 0; element E's bytes are 4*(E+1) before
+// (serialise) or after (deserialise) that.
+//   serialise:   word = [tail of prefix e][payload of e][head of prefix e+1]   (at most these three)
+//   deserialise: word = payload bytes of e, e+1, ... (elements may be shorter than a word)
+template <bool TO_STREAM, bool WORD_OK>
+__device__ __forceinline__ uint32_t compose_word(const unsigned long long* s_off, int nE, int e,
+                                                 unsigned long long rel, unsigned long long e0,
+                                                 const uint8_t* sp) {
+  if (TO_STREAM) {
+    const unsigned long long st = elem_start<true>(s_off, e);
+    const unsigned long long len = s_off[e + 1] - s_off[e];
+    const int r = clamp_u64_to(rel - st, 8);                 // offset of the word inside element e's footprint
+    const int n1 = 4 - r;                                    // lanes [0, n1) hold prefix bytes of e (if r < 4)
+    const int n2 = clamp_u64_to(st + 4 + len - rel, 4);      // lanes [n1, n2) hold payload of e
+    uint32_t w = 0;
+    if (r < 4) w = shr_bytes((uint32_t)len, r) & bytemask(n1);
+    const uint32_t pm = bytemask(n2) & ~bytemask(n1);
+    if (pm) w |= load_word(sp - 4ull * (e0 + e + 1), WORD_OK, pm) & pm;
+    if (n2 < 4 && e + 1 < nE) w |= shl_bytes((uint32_t)(s_off[e + 2] - s_off[e + 1]), n2);
+    return w;
+  } else {
+    uint32_t w = 0;
+    int lane = 0;  // next byte lane to fill
+    while (lane < 4 && e < nE) {
+      const unsigned long long en = s_off[e + 1];
+      const int n = clamp_u64_to(en - rel, 4);  // lanes [lane, n) come from element e
+      if (n > lane) {
+        const uint32_t m = bytemask(n) & ~bytemask(lane);
+        w |= load_word(sp + 4ull * (e0 + e + 1), WORD_OK, m) & m;
+        lane = n;
+      }
+      if (lane < 4) e++;
+    }
+    return w;
+  }
+}
+
+// Builds one boundary chunk (16 aligned output bytes, of which [A, lim) belong to this tile) and
+// stores it. `e` is an element at or before the one that holds the chunk's first in-range byte.
 template <bool TO_STREAM, bool WORD_OK>
 __device__ __forceinline__ void assemble_chunk(const unsigned long long* s_off, int nE, unsigned long long A,
                                                unsigned long long lim, unsigned long long e0, int e,
@@ -126,33 +187,43 @@ __device__ __forceinline__ void assemble_chunk(const unsigned long long* s_off, 
   const unsigned long long cb = q << 4;
   const unsigned long long a = max(cb, A), b = min(cb + 16, lim);
   if (a >= b) return;
-  // e: an element at or before the one holding byte a; walk forward as needed
-  unsigned long long es = A + elem_start<TO_STREAM>(s_off, e);
-  unsigned long long ee = A + elem_start<TO_STREAM>(s_off, e + 1);
-  uint32_t w[4] = {0, 0, 0, 0};
+  const bool full = (a == cb) && (b == cb + 16);
+  uint32_t w[4];
 #pragma unroll
-  for (int bi = 0; bi < 16; bi++) {
-    const unsigned long long p = cb + bi;
-    if (p < a || p >= b) continue;
-    while (ee <= p && e + 1 < nE) {
-      e++;
-      es = ee;
-      ee = A + elem_start<TO_STREAM>(s_off, e + 1);
-    }
-    uint32_t byte;
-    if (TO_STREAM && p < es + 4) {
-      const unsigned long long len = s_off[e + 1] - s_off[e];
-      byte = (uint32_t)(len >> (8 * (p - es))) & 0xffu;
+  for (int wi = 0; wi < 4; wi++) {
+    const unsigned long long wa = cb + 4 * wi;
+    w[wi] = 0;
+    if (wa + 4 <= a || wa >= b) continue;
+    // first in-range byte of this word decides the element; for a word that starts before A (head
+    // of the tile) that byte is A itself
+    const unsigned long long rel = wa >= A ? wa - A : 0;
+    while (e + 1 < nE && elem_start<TO_STREAM>(s_off, e + 1) <= rel) e++;
+    if (wa >= A) {
+      w[wi] = compose_word<TO_STREAM, WORD_OK>(s_off, nE, e, rel, e0, src + (wa - mis));
     } else {
-      const unsigned long long E1 = 4ull * (e0 + e + 1);
-      byte = src[TO_STREAM ? p - mis - E1 : p - mis + E1];
+      // word straddles the tile start: only lanes >= A - wa are ours; compose them byte-wise
+      uint32_t v = 0;
+      int el = e;
+      for (int bi = (int)(A - wa); bi < 4; bi++) {
+        const unsigned long long rb = wa + bi - A;
+        while (el + 1 < nE && elem_start<TO_STREAM>(s_off, el + 1) <= rb) el++;
+        const unsigned long long st = elem_start<TO_STREAM>(s_off, el);
+        uint32_t byte;
+        if (TO_STREAM && rb < st + 4) byte = (uint32_t)((s_off[el + 1] - s_off[el]) >> (8 * (rb - st))) & 0xffu;
+        else byte = src[TO_STREAM ? wa + bi - mis - 4ull * (e0 + el + 1) : wa + bi - mis + 4ull * (e0 + el + 1)];
+        v |= byte << (8 * bi);
+      }
+      w[wi] = v;
     }
-    w[bi >> 2] |= byte << (8 * (bi & 3));
   }
-  if (a == cb && b == cb + 16) {
+  if (full) {
     st_v4(vd + cb, w[0], w[1], w[2], w[3]);
   } else {
-    for (unsigned long long p = a; p < b; p++) vd[p] = (uint8_t)(w[(p - cb) >> 2] >> (8 * (p & 3)));
+#pragma unroll
+    for (int bi = 0; bi < 16; bi++) {
+      const unsigned long long p = cb + bi;
+      if (p >= a && p < b) vd[p] = (uint8_t)(w[bi >> 2] >> (8 * (bi & 3)));
+    }
   }
 }
 
@@ -181,9 +252,10 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
     }
   }
   __syncthreads();
-  // ---- phase A: interior chunks ----------------------------------------------------------------------
+  // ---- phase A: interior chunks, two per thread in flight ------------------------------------------------
   const unsigned long long q0 = (A + 15) >> 4, q1 = lim >> 4;  // chunks fully inside [A, lim)
-  for (unsigned long long q = q0 + threadIdx.x; q < q1; q += blockDim.x) {
+  auto locate = [&](unsigned long long q, const uint8_t*& sp) -> bool {  // interior? -> source pointer
+    if (q >= q1) return false;
     const unsigned long long cb = q << 4;
     const unsigned long long rel = cb - A;
     int e = s_tab[rel >> tsh];
@@ -192,22 +264,32 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
       e++;
       nx = elem_start<TO_STREAM>(s_off, e + 1);
     }
-    const unsigned long long st = elem_start<TO_STREAM>(s_off, e);
-    if (rel + 16 > nx || (TO_STREAM && rel < st + 4)) continue;  // not interior: phase B
+    if (rel + 16 > nx) return false;
+    if (TO_STREAM && rel < elem_start<TO_STREAM>(s_off, e) + 4) return false;
     const unsigned long long E1 = 4ull * (e0 + e + 1);
-    const uint8_t* sp = src + (TO_STREAM ? cb - mis - E1 : cb - mis + E1);
-    uint32_t w0, w1, w2, w3;
-    if (WORD_OK) {
-      w0 = ldg_u32(sp); w1 = ldg_u32(sp + 4); w2 = ldg_u32(sp + 8); w3 = ldg_u32(sp + 12);
-    } else {
-      uint32_t w[4];
+    sp = src + (TO_STREAM ? cb - mis - E1 : cb - mis + E1);
+    return true;
+  };
+  constexpr int kFly = 4;  // chunks in flight per thread: all loads are issued before the first store
+  for (unsigned long long q = q0 + threadIdx.x; q < q1; q += (unsigned long long)kFly * blockDim.x) {
+    const uint8_t* sp[kFly];
+    bool ok[kFly];
+    uint32_t w[kFly][4];
 #pragma unroll
-      for (int k = 0; k < 4; k++)
-        w[k] = (uint32_t)sp[4 * k] | ((uint32_t)sp[4 * k + 1] << 8) | ((uint32_t)sp[4 * k + 2] << 16) |
-               ((uint32_t)sp[4 * k + 3] << 24);
-      w0 = w[0]; w1 = w[1]; w2 = w[2]; w3 = w[3];
+    for (int f = 0; f < kFly; f++) {
+      sp[f] = src;
+      ok[f] = locate(q + (unsigned long long)f * blockDim.x, sp[f]);
     }
-    st_v4(vd + cb, w0, w1, w2, w3);
+#pragma unroll
+    for (int f = 0; f < kFly; f++) {
+      if (ok[f]) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) w[f][k] = load_word(sp[f] + 4 * k, WORD_OK);
+      }
+    }
+#pragma unroll
+    for (int f = 0; f < kFly; f++)
+      if (ok[f]) st_v4(vd + ((q + (unsigned long long)f * blockDim.x) << 4), w[f][0], w[f][1], w[f][2], w[f][3]);
   }
   // ---- phase B: boundary chunks, one owner thread each ------------------------------------------------
   // Boundary points b_e: for TO_STREAM the prefix bytes [hs_e, hs_e + 4) of every element; otherwise
@@ -249,7 +331,7 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
 // LEN_SIZE: 4 or 8 bytes per length; FIXED: lengths come from fixed-width rows (trailing NULs
 // stripped) and the payload of element i starts at i * width instead of being packed.
 template <int LEN_SIZE, bool FIXED, bool WORD_OK>
-__global__ void __launch_bounds__(kSerThreads)
+__global__ void __launch_bounds__(kSerThreads, 4)
 k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ lengths,
                   unsigned long long n, uint32_t width, uint8_t* __restrict__ dst,
                   unsigned long long dst_capacity, unsigned long long* __restrict__ ws,
@@ -649,7 +731,7 @@ constexpr int kGatTile = 1024;
 constexpr int kGatThreads = 256;
 
 template <bool WORD_OK>
-__global__ void __launch_bounds__(kGatThreads)
+__global__ void __launch_bounds__(kGatThreads, 4)
 k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ offsets,
              const unsigned long long* __restrict__ hdr, uint8_t* __restrict__ blob,
              unsigned long long blob_capacity) {
