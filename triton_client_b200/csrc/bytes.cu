@@ -429,9 +429,10 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
 // =================================================================================================
 // deserialise
 // =================================================================================================
-constexpr int kDesChunk = 8192;    // bytes of stream per chunk
+constexpr int kDesChunk = 16384;   // bytes of stream per chunk
 constexpr int kDesWindow = 512;    // look-behind window for the entry guess
-constexpr int kDesThreads = 128;
+constexpr int kDesWarps = 4;       // warps per CTA of k_des_speculate; one warp = 32 consecutive chunks
+constexpr int kDesThreads = kDesWarps * 32;
 constexpr int kDesListCap = 512;   // header positions recorded per chunk (uint16, chunk-relative)
 constexpr unsigned long long kNoGuess = ~0ull;
 
@@ -455,84 +456,87 @@ struct DesArrays {
   unsigned short* list;      // [K][kDesListCap] chunk-relative header positions
 };
 
-__device__ __forceinline__ uint32_t lds_u32_unaligned(const uint32_t* s, uint32_t byte_off) {
-  const uint32_t lo = s[byte_off >> 2], hi = s[(byte_off >> 2) + 1];
-  return __funnelshift_r(lo, hi, (byte_off & 3) * 8);
+// Little-endian uint32 at an arbitrary byte position of the stream: two aligned word loads (both
+// normally L1 hits) and a funnel shift. The second word is only read when the value straddles.
+__device__ __forceinline__ uint32_t ldg_u32_unaligned(const uint8_t* __restrict__ base_aligned4,
+                                                      unsigned long long pos) {
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(base_aligned4) + (pos >> 2);
+  const uint32_t lo = __ldg(w);
+  const unsigned sh = (unsigned)(pos & 3) * 8;
+  if (sh == 0) return lo;
+  return __funnelshift_r(lo, __ldg(w + 1), sh);
 }
 
-// Per chunk: stage [chunk start - window, chunk end + 4) in shared memory, vote for the entry
-// header, chase the chunk's chain.
+// Speculative chunk chase. One warp owns 32 consecutive chunks:
+//   1. entry guess, warp-cooperative, one chunk at a time: the 32 lanes chase from every byte of
+//      the chunk's 512-byte look-behind window (consecutive candidates -> coalesced loads) to the
+//      chunk start and vote on where they land; the plurality (ties: smallest offset) is the guess;
+//   2. main chase, lane-parallel: lane l follows the chain of chunk l straight from global memory,
+//      so one warp instruction advances 32 independent chains (a per-CTA serial chase spent 31 of
+//      32 lanes idle and made this kernel instruction-bound), recording header positions.
+// Exactness does not depend on the guess: k_des_verify checks entry[k] == exit[k-1] for all k.
+// stream4 = stream rounded down to a 4-byte boundary, bias = stream - stream4 (0..3).
 __global__ void __launch_bounds__(kDesThreads)
-k_des_speculate(const uint8_t* __restrict__ stream, unsigned long long S, unsigned long long K,
-                DesArrays A) {
-  constexpr int kStage = kDesWindow + kDesChunk + 16;
-  __shared__ __align__(16) uint32_t s_buf[kStage / 4 + 2];
-  __shared__ unsigned int s_votes[kDesWindow];
-  __shared__ unsigned int s_best;
-  const unsigned long long k = blockIdx.x;
-  const unsigned long long c0 = k * kDesChunk;                       // chunk start
-  const unsigned long long c1 = min(c0 + kDesChunk, S);              // chunk end
-  const unsigned long long lo = c0 >= kDesWindow ? c0 - kDesWindow : 0;
-  const unsigned long long hi = min(c1 + 16, S);
-  // stage (stream base + lo is 16-byte aligned when the stream base is: lo is a multiple of 512)
-  const bool aligned = (reinterpret_cast<uintptr_t>(stream) & 15) == 0;
-  const int nbytes = (int)(hi - lo);
-  if (aligned) {
-    const uint4* src = reinterpret_cast<const uint4*>(stream + lo);
-    uint4* d4 = reinterpret_cast<uint4*>(s_buf);
-    const int nvec = nbytes >> 4;
-    for (int i = threadIdx.x; i < nvec; i += kDesThreads) d4[i] = __ldg(src + i);
-    uint8_t* d8 = reinterpret_cast<uint8_t*>(s_buf);
-    for (int i = (nvec << 4) + threadIdx.x; i < nbytes; i += kDesThreads) d8[i] = stream[lo + i];
-  } else {
-    uint8_t* d8 = reinterpret_cast<uint8_t*>(s_buf);
-    for (int i = threadIdx.x; i < nbytes; i += kDesThreads) d8[i] = stream[lo + i];
-  }
-  for (int i = threadIdx.x; i < kDesWindow; i += kDesThreads) s_votes[i] = 0;
-  if (threadIdx.x == 0) s_best = 0;
-  __syncthreads();
+k_des_speculate(const uint8_t* __restrict__ stream4, unsigned int bias, unsigned long long S,
+                unsigned long long K, DesArrays A) {
+  __shared__ unsigned int s_votes[kDesWarps][kDesWindow];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned long long kbase = ((unsigned long long)blockIdx.x * kDesWarps + warp) * 32;
+  if (kbase >= K) return;
+  unsigned int* votes = s_votes[warp];
+  auto load_len = [&](unsigned long long pos) { return ldg_u32_unaligned(stream4, pos + bias); };
 
-  unsigned long long g = 0;
-  if (k > 0) {
-    // every byte of the look-behind window is a candidate header; chase each to the chunk start
-    for (unsigned long long p0 = lo + threadIdx.x; p0 < c0; p0 += kDesThreads) {
-      unsigned long long pos = p0;
+  unsigned long long my_g = kNoGuess;
+  for (int j = 0; j < 32; j++) {
+    const unsigned long long k = kbase + j;
+    if (k >= K) break;
+    if (k == 0) {
+      if (lane == j) my_g = 0;
+      continue;
+    }
+    const unsigned long long c0 = k * kDesChunk;
+    for (int i = lane; i < kDesWindow; i += 32) votes[i] = 0;
+    __syncwarp();
+    for (int it = 0; it < kDesWindow / 32; it++) {
+      unsigned long long pos = c0 - kDesWindow + it * 32 + lane;
       bool ok = true;
       while (pos < c0) {
         if (pos + 4 > S) { ok = false; break; }
-        const unsigned long long nx = pos + 4 + lds_u32_unaligned(s_buf, (uint32_t)(pos - lo));
+        const unsigned long long nx = pos + 4 + load_len(pos);
         if (nx > S) { ok = false; break; }
         pos = nx;
       }
-      if (ok && pos - c0 < kDesWindow) atomicAdd(&s_votes[pos - c0], 1u);
+      if (ok && pos - c0 < kDesWindow) atomicAdd(&votes[pos - c0], 1u);
     }
-    __syncthreads();
-    // plurality vote, ties to the smallest offset
+    __syncwarp();
     unsigned int best = 0;
-    for (int i = threadIdx.x; i < kDesWindow; i += kDesThreads) {
-      const unsigned int v = s_votes[i];
+    for (int i = lane; i < kDesWindow; i += 32) {
+      const unsigned int v = votes[i];
       if (v) best = max(best, (v << 16) | (unsigned int)(kDesWindow - 1 - i));
     }
-    atomicMax(&s_best, best);
-    __syncthreads();
-    g = s_best ? c0 + (kDesWindow - 1 - (s_best & 0xffffu)) : kNoGuess;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == j) my_g = best ? c0 + (kDesWindow - 1 - (best & 0xffffu)) : kNoGuess;
+    __syncwarp();
   }
-  if (threadIdx.x == 0) {
-    unsigned long long pos = g;
-    unsigned int n = 0, err = 0;
-    unsigned short* list = A.list + k * kDesListCap;
-    if (g != kNoGuess) {
-      while (pos < c1) {
-        if (pos + 4 > S) { err = 1; break; }
-        const unsigned long long nx = pos + 4 + lds_u32_unaligned(s_buf, (uint32_t)(pos - lo));
-        if (nx > S) { err = 1; break; }
-        if (n < kDesListCap) list[n] = (unsigned short)(pos - c0);
-        n++;
-        pos = nx;
-      }
+  // main chase: lane -> chunk kbase + lane
+  const unsigned long long k = kbase + lane;
+  if (k >= K) return;
+  const unsigned long long c0 = k * kDesChunk, c1 = min(c0 + kDesChunk, S);
+  unsigned long long pos = my_g;
+  unsigned int n = 0, err = 0;
+  unsigned short* list = A.list + k * kDesListCap;
+  if (my_g != kNoGuess) {
+    while (pos < c1) {
+      if (pos + 4 > S) { err = 1; break; }
+      const unsigned long long nx = pos + 4 + load_len(pos);
+      if (nx > S) { err = 1; break; }
+      if (n < kDesListCap) list[n] = (unsigned short)(pos - c0);
+      n++;
+      pos = nx;
     }
-    A.g[k] = g; A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
   }
+  A.g[k] = my_g; A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
 }
 
 // One chase step straight from global memory (sweep / overflow paths).
@@ -880,7 +884,11 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
   A.list = reinterpret_cast<unsigned short*>(p);
   const uint8_t* st = static_cast<const uint8_t*>(stream_dev);
   TCB_CUDA(cudaMemsetAsync(hdr, 0, 256, s));
-  k_des_speculate<<<(unsigned)K, kDesThreads, 0, s>>>(st, stream_bytes, K, A);
+  {
+    const unsigned int bias = (unsigned int)(reinterpret_cast<uintptr_t>(st) & 3);
+    const unsigned long long warps = (K + 31) / 32;
+    k_des_speculate<<<(unsigned)((warps + kDesWarps - 1) / kDesWarps), kDesThreads, 0, s>>>(st - bias, bias, stream_bytes, K, A);
+  }
   auto resolve = [&]() -> cudaError_t {
     // first mismatch / first error start at ~0 (atomicMin), the scan workspace at 0
     cudaMemsetAsync(hdr + DW_FIRST, 0xFF, 8, s);
