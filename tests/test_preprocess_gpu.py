@@ -147,3 +147,95 @@ def test_full_size_properties_cfg3():
         ref = oracle_preprocess(batch[i].cpu().numpy(), 3, 224, 224, 2, "FP32", "VGG")
         assert np.array_equal(out[i].cpu().numpy(), ref)
     plan.close()
+
+
+def test_fused_and_two_pass_paths_agree_on_random_geometries():
+    """The fused kernel (path=2) and the general two-pass kernels (path=1) are independent
+    implementations; on geometries both accept they must agree bit for bit (and with the oracle
+    on a sample)."""
+    import torch
+
+    from triton_client_b200.image_client import PreprocessPlan
+
+    from triton_client_b200 import _lib
+
+    rng = np.random.default_rng(99)
+    n_both = 0
+    for trial in range(16):
+        W, H = int(rng.integers(230, 2600)), int(rng.integers(230, 1500))
+        w, h = int(rng.choice([224, 299, 160, 64])), int(rng.choice([224, 299, 192, 48]))
+        cin = int(rng.choice([1, 3, 4]))
+        c = 1 if cin == 1 else int(rng.choice([1, 3]))
+        fmt, dt = int(rng.choice([1, 2])), str(rng.choice(["FP32", "FP16", "UINT8", "FP64"]))
+        sc = str(rng.choice(["NONE", "INCEPTION", "VGG"]))
+        if dt == "UINT8" and sc == "VGG" and c == 1:
+            sc = "NONE"
+        src = rng.integers(0, 256, (H, W, cin), dtype=np.uint8)
+        d_src = torch.from_numpy(src).cuda()
+        outs = []
+        for path in (1, 2):
+            plan = PreprocessPlan([(W, H, cin)], fmt, dt, c, h, w, sc, device=0, path=path)
+            out = torch.zeros(plan.out_bytes_per_image, dtype=torch.uint8, device="cuda")
+            try:
+                plan.run([d_src.data_ptr()], out.data_ptr(), out.numel())
+            except _lib.TcbError as ex:   # e.g. more filter taps than the fused kernel's classes cover
+                assert path == 2 and ex.code == _lib.TCB_ERR_UNSUPPORTED
+                break
+            torch.cuda.synchronize()
+            assert plan.info()["fused_images"] == (1 if path == 2 else 0)
+            outs.append(out.cpu().numpy())
+            plan.close()
+        if len(outs) < 2:
+            continue
+        n_both += 1
+        assert np.array_equal(outs[0], outs[1]), (W, H, w, h, cin, c, fmt, dt, sc)
+        if trial % 3 == 0:
+            lutdt = pb.scaling_lut(dt, c, sc).dtype
+            ref = oracle_preprocess(src, c, h, w, fmt, dt, sc)
+            assert np.array_equal(outs[1].view(lutdt).reshape(ref.shape), ref)
+    assert n_both >= 8
+
+
+def test_fused_path_refuses_what_it_cannot_do():
+    import torch
+
+    from triton_client_b200 import _lib
+    from triton_client_b200.image_client import PreprocessPlan
+
+    src = torch.zeros((224, 300, 3), dtype=torch.uint8, device="cuda")  # height unchanged: single-axis
+    plan = PreprocessPlan([(300, 224, 3)], 2, "FP32", 3, 224, 224, "NONE", device=0, path=2)
+    out = torch.zeros(3 * 224 * 224 * 4, dtype=torch.uint8, device="cuda")
+    with pytest.raises(_lib.TcbError) as ei:
+        plan.run([src.data_ptr()], out.data_ptr(), out.numel())
+    assert ei.value.code == _lib.TCB_ERR_UNSUPPORTED and "fused" in ei.value.msg
+
+
+def test_unaligned_and_pitched_sources():
+    """Sources whose rows are not 4/16-byte aligned (odd widths in a packed batch) and sources with
+    a row pitch take the byte-wise de-interleave inside the fused kernel; results are unchanged."""
+    import torch
+
+    from triton_client_b200.image_client import PreprocessPlan
+
+    rng = np.random.default_rng(5)
+    W, H = 641, 479
+    packed = rng.integers(0, 256, (3, H, W, 3), dtype=np.uint8)          # images 1, 2 start unaligned
+    d_packed = torch.from_numpy(packed).cuda()
+    plan = PreprocessPlan([(W, H, 3)] * 3, 1, "FP16", 3, 224, 224, "INCEPTION", device=0)
+    out = torch.zeros(3 * plan.out_bytes_per_image, dtype=torch.uint8, device="cuda")
+    plan.run([d_packed.data_ptr() + i * H * W * 3 for i in range(3)], out.data_ptr(), out.numel())
+    torch.cuda.synchronize()
+    got = out.cpu().numpy().view(np.float16).reshape(3, 224, 224, 3)
+    for i in range(3):
+        assert np.array_equal(got[i], oracle_preprocess(packed[i], 3, 224, 224, 1, "FP16", "INCEPTION"))
+    plan.close()
+    pitch = 2048                                                          # pitched rows
+    wide = rng.integers(0, 256, (480, pitch), dtype=np.uint8)
+    d_wide = torch.from_numpy(wide).cuda()
+    plan = PreprocessPlan([(640, 480, 3, pitch)], 2, "FP32", 3, 224, 224, "VGG", device=0)
+    out = torch.zeros(plan.out_bytes_per_image, dtype=torch.uint8, device="cuda")
+    plan.run([d_wide.data_ptr()], out.data_ptr(), out.numel())
+    torch.cuda.synchronize()
+    ref = oracle_preprocess(wide[:, : 640 * 3].reshape(480, 640, 3), 3, 224, 224, 2, "FP32", "VGG")
+    assert np.array_equal(out.cpu().numpy().view(np.float32).reshape(3, 224, 224), ref)
+    plan.close()

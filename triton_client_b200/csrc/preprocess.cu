@@ -357,10 +357,11 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
     int band = 0; size_t smem = 0;
     const bool can_fuse = path != 1 && fused_supported(*p, d, &band, &smem);
     if (path == 2 && !can_fuse) {
+      const int fw = d.W, fh = d.H, fc = d.cin, fp = d.pitch;
       delete p;
       return set_error(TCB_ERR_UNSUPPORTED,
                        "TcbPreprocessPlanCreate: image %d (%dx%d, %d ch, pitch %d) does not fit the "
-                       "fused kernel", i, d.W, d.H, d.cin, d.pitch);
+                       "fused kernel", i, fw, fh, fc, fp);
     }
     if (can_fuse) {
       d.fused = 1; d.band_rows = band;
