@@ -278,26 +278,41 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
     }
   };
 
-  // vertical pass of output row yy (all groups it needs are in the ring)
+  // vertical pass of output row yy (all groups it needs are in the ring). One unit = 4 consecutive
+  // output elements (one 16-byte tmp4 load per group, 128-bit store for 4-byte elements). Everything
+  // that depends only on the thread (unit -> line/column, table rows, destination offset) is
+  // computed once, above the row loop.
+  int v_i0 = 0, v_c0 = 0, v_c1 = 0, v_c2 = 0, v_c3 = 0;
+  size_t v_e0 = 0;              // element offset of the unit at yy = 0
+  const size_t v_erow = nchw ? (size_t)out_w : (size_t)L;  // element offset increment per output row
+  if (vec4 && tid < n_units) {
+    if (nchw) {
+      v_i0 = my_ln * out_w + 4 * my_x4;
+      v_e0 = (size_t)my_ln * out_h * out_w + 4 * my_x4;
+      v_c0 = v_c1 = v_c2 = v_c3 = my_ln * 256;
+    } else {
+      v_i0 = 4 * tid;
+      v_e0 = (size_t)v_i0;
+      if (C == 3) {
+        const int c0 = tid % 3;  // (4 * tid) % 3
+        const int c1 = c0 == 2 ? 0 : c0 + 1, c2 = c1 == 2 ? 0 : c1 + 1;
+        v_c0 = c0 * 256; v_c1 = c1 * 256; v_c2 = c2 * 256; v_c3 = c0 * 256;
+      }
+    }
+  }
   auto vertical = [&](int yy) {
     const int gv0 = vg[2 * yy];
     const int32_t* vc = pool + d.vc_off + (size_t)yy * d.nwv * 3;
     const int slot0 = (gv0 - g_first) % ng;
     if (vec4) {
-      for (int u4 = tid; u4 < n_units; u4 += nthreads) {
-        int ln = my_ln, x4 = my_x4;
-        if (u4 != tid) {
-          ln = 0; x4 = u4;
-          if (nchw) { ln = u4 / upl; x4 = u4 - ln * upl; }
-        }
-        const int i0 = nchw ? ln * out_w + 4 * x4 : 4 * x4;  // word index inside a slot
+      if (tid < n_units) {  // first (normally only) unit of this thread: hoisted constants
         uint32_t a[4][3];
 #pragma unroll
-        for (int v = 0; v < 4; v++) { a[v][0] = 0; a[v][1] = 0; a[v][2] = 0; }
+        for (int v = 0; v < 4; v++) { a[v][0] = 1u << (kPrecisionBits - 1); a[v][1] = 0; a[v][2] = 0; }
         int slot = slot0;
         for (int j = 0; j < d.nwv; j++) {
-          const uint32_t k0 = vc[3 * j], k1 = vc[3 * j + 1], k2 = vc[3 * j + 2];
-          const uint4 px = *reinterpret_cast<const uint4*>(tmp4 + (size_t)slot * L + i0);
+          const uint32_t k0 = __ldg(vc + 3 * j), k1 = __ldg(vc + 3 * j + 1), k2 = __ldg(vc + 3 * j + 2);
+          const uint4 px = *reinterpret_cast<const uint4*>(tmp4 + (size_t)slot * L + v_i0);
           a[0][0] = __dp4a(px.x, k0, a[0][0]); a[0][1] = __dp4a(px.x, k1, a[0][1]); a[0][2] = __dp4a(px.x, k2, a[0][2]);
           a[1][0] = __dp4a(px.y, k0, a[1][0]); a[1][1] = __dp4a(px.y, k1, a[1][1]); a[1][2] = __dp4a(px.y, k2, a[1][2]);
           a[2][0] = __dp4a(px.z, k0, a[2][0]); a[2][1] = __dp4a(px.z, k1, a[2][1]); a[2][2] = __dp4a(px.z, k2, a[2][2]);
@@ -306,58 +321,64 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
         }
         uint32_t u[4];
 #pragma unroll
-        for (int v = 0; v < 4; v++) {
-          const uint32_t acc = (1u << (kPrecisionBits - 1)) + a[v][0] + (a[v][1] << 8) + (a[v][2] << 16);
-          u[v] = min(acc >> kPrecisionBits, 255u);
-        }
-        size_t e0;
-        int chv[4];
-        if (nchw) {
-          e0 = ((size_t)ln * out_h + yy) * out_w + 4 * x4;
-          chv[0] = chv[1] = chv[2] = chv[3] = ln;
-        } else {
-          e0 = (size_t)yy * L + i0;
-          if (C == 3) {
-            const int c0 = x4 % 3;  // (4 * x4) % 3
-            chv[0] = c0; chv[1] = c0 == 2 ? 0 : c0 + 1; chv[2] = chv[1] == 2 ? 0 : chv[1] + 1; chv[3] = c0;
-          } else {
-            chv[0] = chv[1] = chv[2] = chv[3] = 0;
-          }
-        }
+        for (int v = 0; v < 4; v++) u[v] = min((a[v][0] + (a[v][1] << 8) + (a[v][2] << 16)) >> kPrecisionBits, 255u);
+        const size_t e0 = v_e0 + (size_t)yy * v_erow;
         if (elem == 4) {
           const uint32_t* l32 = reinterpret_cast<const uint32_t*>(lut);
-          st_global_v4(dimg + e0 * 4, __ldg(l32 + chv[0] * 256 + u[0]), __ldg(l32 + chv[1] * 256 + u[1]),
-                       __ldg(l32 + chv[2] * 256 + u[2]), __ldg(l32 + chv[3] * 256 + u[3]));
+          st_global_v4(dimg + e0 * 4, __ldg(l32 + v_c0 + u[0]), __ldg(l32 + v_c1 + u[1]), __ldg(l32 + v_c2 + u[2]),
+                       __ldg(l32 + v_c3 + u[3]));
         } else if (elem == 2) {
           const uint16_t* l16 = reinterpret_cast<const uint16_t*>(lut);
-          const uint32_t lo = __ldg(l16 + chv[0] * 256 + u[0]) | ((uint32_t)__ldg(l16 + chv[1] * 256 + u[1]) << 16);
-          const uint32_t hi = __ldg(l16 + chv[2] * 256 + u[2]) | ((uint32_t)__ldg(l16 + chv[3] * 256 + u[3]) << 16);
+          const uint32_t lo = __ldg(l16 + v_c0 + u[0]) | ((uint32_t)__ldg(l16 + v_c1 + u[1]) << 16);
+          const uint32_t hi = __ldg(l16 + v_c2 + u[2]) | ((uint32_t)__ldg(l16 + v_c3 + u[3]) << 16);
           st_global_v2(dimg + e0 * 2, lo, hi);
         } else if (elem == 1) {
-          const uint32_t w = __ldg(lut + chv[0] * 256 + u[0]) | ((uint32_t)__ldg(lut + chv[1] * 256 + u[1]) << 8) |
-                             ((uint32_t)__ldg(lut + chv[2] * 256 + u[2]) << 16) |
-                             ((uint32_t)__ldg(lut + chv[3] * 256 + u[3]) << 24);
+          const uint32_t w = __ldg(lut + v_c0 + u[0]) | ((uint32_t)__ldg(lut + v_c1 + u[1]) << 8) |
+                             ((uint32_t)__ldg(lut + v_c2 + u[2]) << 16) | ((uint32_t)__ldg(lut + v_c3 + u[3]) << 24);
           *reinterpret_cast<uint32_t*>(dimg + e0) = w;
         } else {
           const uint2* l64 = reinterpret_cast<const uint2*>(lut);
-          const uint2 q0 = __ldg(l64 + chv[0] * 256 + u[0]), q1 = __ldg(l64 + chv[1] * 256 + u[1]);
-          const uint2 q2 = __ldg(l64 + chv[2] * 256 + u[2]), q3 = __ldg(l64 + chv[3] * 256 + u[3]);
+          const uint2 q0 = __ldg(l64 + v_c0 + u[0]), q1 = __ldg(l64 + v_c1 + u[1]);
+          const uint2 q2 = __ldg(l64 + v_c2 + u[2]), q3 = __ldg(l64 + v_c3 + u[3]);
           st_global_v4(dimg + e0 * 8, q0.x, q0.y, q1.x, q1.y);
           st_global_v4(dimg + e0 * 8 + 16, q2.x, q2.y, q3.x, q3.y);
         }
       }
+      // further units (only when a row has more than blockDim units): word by word below
+      for (int i = 4 * nthreads + 4 * tid; i < 4 * n_units; i += 4 * nthreads) {
+#pragma unroll 1
+        for (int v = 0; v < 4; v++) {
+          const int iw = i + v;
+          uint32_t a0 = 1u << (kPrecisionBits - 1), a1 = 0, a2 = 0;
+          int slot = slot0;
+          for (int j = 0; j < d.nwv; j++) {
+            const uint32_t px = tmp4[(size_t)slot * L + iw];
+            a0 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j), a0); a1 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 1), a1);
+            a2 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 2), a2);
+            if (++slot == ng) slot = 0;
+          }
+          const uint32_t u = min((a0 + (a1 << 8) + (a2 << 16)) >> kPrecisionBits, 255u);
+          size_t e; int ch;
+          if (nchw) { ch = iw / out_w; e = ((size_t)ch * out_h + yy) * out_w + (iw - ch * out_w); }
+          else { ch = iw % C; e = (size_t)yy * L + iw; }
+          const uint8_t* le = lut + ((size_t)ch * 256 + u) * elem;
+          if (elem == 4) reinterpret_cast<uint32_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint32_t*>(le));
+          else if (elem == 2) reinterpret_cast<uint16_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint16_t*>(le));
+          else if (elem == 1) dimg[e] = __ldg(le);
+          else reinterpret_cast<unsigned long long*>(dimg)[e] = __ldg(reinterpret_cast<const unsigned long long*>(le));
+        }
+      }
     } else {
       for (int i = tid; i < L; i += nthreads) {
-        uint32_t a0 = 0, a1 = 0, a2 = 0;
+        uint32_t a0 = 1u << (kPrecisionBits - 1), a1 = 0, a2 = 0;
         int slot = slot0;
         for (int j = 0; j < d.nwv; j++) {
           const uint32_t px = tmp4[(size_t)slot * L + i];
-          a0 = __dp4a(px, (uint32_t)vc[3 * j], a0); a1 = __dp4a(px, (uint32_t)vc[3 * j + 1], a1);
-          a2 = __dp4a(px, (uint32_t)vc[3 * j + 2], a2);
+          a0 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j), a0); a1 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 1), a1);
+          a2 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 2), a2);
           if (++slot == ng) slot = 0;
         }
-        const uint32_t acc = (1u << (kPrecisionBits - 1)) + a0 + (a1 << 8) + (a2 << 16);
-        const uint32_t u = min(acc >> kPrecisionBits, 255u);
+        const uint32_t u = min((a0 + (a1 << 8) + (a2 << 16)) >> kPrecisionBits, 255u);
         size_t e;
         int ch;
         if (nchw) { ch = i / out_w; e = ((size_t)ch * out_h + yy) * out_w + (i - ch * out_w); }
@@ -378,47 +399,47 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   if (tid == 0 && n_groups > 2) issue(2);
 
   int slot = 0;
-  for (int i = 0; i < n_groups; i++) {
+  for (int i = 0; i <= n_groups; i++) {  // the last iteration only drains the vertical pass
     const int g = g_first + i;
-    // (a) de-interleave the next group into the other P4 buffer
-    if (i + 1 < n_groups) {
-      mbar_wait(&bars[(i + 1) & 1], ((i + 1) >> 1) & 1);
-      deinterleave(i + 1);
-    }
-    // (b) horizontal pass of group g: 4 rows x C channels per thread
-    if (xx < out_w) {
-      const uint4* Pb = P4 + (size_t)(i & 1) * C * wqp;
-      uint32_t* out = tmp4 + (size_t)slot * L + tmp_idx0;
+    if (i < n_groups) {
+      // (a) de-interleave the next group into the other P4 buffer
+      if (i + 1 < n_groups) {
+        mbar_wait(&bars[(i + 1) & 1], ((i + 1) >> 1) & 1);
+        deinterleave(i + 1);
+      }
+      // (b) horizontal pass of group g: 4 rows x C channels per thread
+      if (xx < out_w) {
+        const uint4* Pb = P4 + (size_t)(i & 1) * C * wqp;
+        uint32_t* out = tmp4 + (size_t)slot * L + tmp_idx0;
 #pragma unroll
-      for (int ch = 0; ch < C; ch++) {
-        uint32_t a[4][3];
+        for (int ch = 0; ch < C; ch++) {
+          uint32_t a[4][3];
 #pragma unroll
-        for (int r = 0; r < 4; r++) { a[r][0] = 0; a[r][1] = 0; a[r][2] = 0; }
-        const uint4* p = Pb + ch * wqp;
+          for (int r = 0; r < 4; r++) { a[r][0] = 1u << (kPrecisionBits - 1); a[r][1] = 0; a[r][2] = 0; }
+          const uint4* p = Pb + ch * wqp;
 #pragma unroll
-        for (int j = 0; j < NW; j++) {
-          const uint4 v = p[poff[j]];
-          a[0][0] = __dp4a(v.x, kc[j][0], a[0][0]); a[0][1] = __dp4a(v.x, kc[j][1], a[0][1]); a[0][2] = __dp4a(v.x, kc[j][2], a[0][2]);
-          a[1][0] = __dp4a(v.y, kc[j][0], a[1][0]); a[1][1] = __dp4a(v.y, kc[j][1], a[1][1]); a[1][2] = __dp4a(v.y, kc[j][2], a[1][2]);
-          a[2][0] = __dp4a(v.z, kc[j][0], a[2][0]); a[2][1] = __dp4a(v.z, kc[j][1], a[2][1]); a[2][2] = __dp4a(v.z, kc[j][2], a[2][2]);
-          a[3][0] = __dp4a(v.w, kc[j][0], a[3][0]); a[3][1] = __dp4a(v.w, kc[j][1], a[3][1]); a[3][2] = __dp4a(v.w, kc[j][2], a[3][2]);
+          for (int j = 0; j < NW; j++) {
+            const uint4 v = p[poff[j]];
+            a[0][0] = __dp4a(v.x, kc[j][0], a[0][0]); a[0][1] = __dp4a(v.x, kc[j][1], a[0][1]); a[0][2] = __dp4a(v.x, kc[j][2], a[0][2]);
+            a[1][0] = __dp4a(v.y, kc[j][0], a[1][0]); a[1][1] = __dp4a(v.y, kc[j][1], a[1][1]); a[1][2] = __dp4a(v.y, kc[j][2], a[1][2]);
+            a[2][0] = __dp4a(v.z, kc[j][0], a[2][0]); a[2][1] = __dp4a(v.z, kc[j][1], a[2][1]); a[2][2] = __dp4a(v.z, kc[j][2], a[2][2]);
+            a[3][0] = __dp4a(v.w, kc[j][0], a[3][0]); a[3][1] = __dp4a(v.w, kc[j][1], a[3][1]); a[3][2] = __dp4a(v.w, kc[j][2], a[3][2]);
+          }
+          uint32_t u[4];
+#pragma unroll
+          for (int r = 0; r < 4; r++) u[r] = min((a[r][0] + (a[r][1] << 8) + (a[r][2] << 16)) >> kPrecisionBits, 255u);
+          out[ch * tmp_chs] = __byte_perm(__byte_perm(u[0], u[1], 0x0040), __byte_perm(u[2], u[3], 0x0040), 0x5410);
         }
-        uint32_t u[4];
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-          const uint32_t acc = (1u << (kPrecisionBits - 1)) + a[r][0] + (a[r][1] << 8) + (a[r][2] << 16);
-          u[r] = min(acc >> kPrecisionBits, 255u);
-        }
-        out[ch * tmp_chs] = __byte_perm(__byte_perm(u[0], u[1], 0x0040), __byte_perm(u[2], u[3], 0x0040), 0x5410);
       }
     }
-    // (c) vertical pass of the rows whose last group was written in the previous phase
+    // (c) vertical pass of the rows whose last group was written in an earlier phase
     while (yy_next < yy1 && vg[2 * yy_next + 1] < g) vertical(yy_next++);
-    __syncthreads();
-    if (tid == 0 && i + 3 < n_groups) issue(i + 3);  // stage (i+1)&1 was drained in (a)
-    if (++slot == ng) slot = 0;
+    if (i < n_groups) {
+      __syncthreads();
+      if (tid == 0 && i + 3 < n_groups) issue(i + 3);  // stage (i+1)&1 was drained in (a)
+      if (++slot == ng) slot = 0;
+    }
   }
-  while (yy_next < yy1) vertical(yy_next++);
 }
 
 // ---- host side ---------------------------------------------------------------------------------------
