@@ -33,6 +33,15 @@ CFG3 = {"n": 256, "W": 1920, "H": 1080, "c": 3, "h": 224, "w": 224, "format": 2,
 CFG3_ALGO_BYTES_PER_IMAGE = 1920 * 1080 * 3 + 3 * 224 * 224 * 4  # 6 822 912
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
+    capture (profiles/traffic.json), or None."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def measured_peak_hbm():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -122,6 +131,11 @@ def cpu_preprocess_rate(images_per_worker, workers):
     return workers * images_per_worker / dt, dt
 
 
+def cpu_images_per_worker(workers):
+    """Bounded sample: about 15 s of CPU work per step (a 1080p image costs ~11-17 ms per core)."""
+    return max(4, int(15.0 / 0.013 / max(workers, 1)))
+
+
 def usable_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -136,7 +150,7 @@ def run_reference(args, rank, world):
         return
     cores = usable_cores()
     workers = max(1, cores)
-    per = max(2, int(round(4 * 32 / max(workers, 32))) if workers >= 32 else 8)
+    per = cpu_images_per_worker(workers)
     total_steps = args.warmup + args.steps
     rates = []
     t_all = time.perf_counter()
@@ -195,7 +209,7 @@ def bench_bytes(torch, dev, peak, steps, warmup):
         "metric": "BYTES serialize GB/s", "value": (P + 4 * N) / t / 1e9, "unit": "GB/s of serialized output",
         "us_per_launch": t * 1e6, "elements": N,
         "roofline": {"bound": "hbm", "achieved": algo / t / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": algo / t / 1e9 / peak, "traffic": None},
+                     "frac": algo / t / 1e9 / peak, "traffic": ncu_traffic("k_bytes_serialize_cfg2")},
         "config": {"workload": "cfg2: 1M strings len~U[0,256] (G-BYTES seed 42), device blob+int32 lengths -> device buffer",
                    "l2": "256 MiB flush write between iterations", "includes": "workspace memset + scan+scatter kernel"}}
     # cfg4: deserialize 16M strings (~2.1 GB); stream generated on the device by the serializer
@@ -224,7 +238,7 @@ def bench_bytes(torch, dev, peak, steps, warmup):
         "metric": "BYTES deserialize GB/s", "value": tot4 / t / 1e9, "unit": "GB/s of serialized input",
         "ms_per_call": t * 1e3, "elements": N4, "roundtrip_bit_exact": ok,
         "roofline": {"bound": "hbm", "achieved": algo4 / t / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": algo4 / t / 1e9 / peak, "traffic": None},
+                     "frac": algo4 / t / 1e9 / peak, "traffic": ncu_traffic("deserialize_cfg4_all_kernels")},
         "config": {"workload": "cfg4: 16M strings len~U[0,256] (~2.1 GB stream) -> int64 offsets + compact payload, all on device",
                    "l2": "input 2.1 GB >> L2", "includes": "all deserialize kernels + the 3 small D2H header reads the call makes"}}
     del stream4, blob4, lens4, offsets, payload
@@ -256,7 +270,7 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = usable_cores()
-        per = 8 if cores < 32 else 4
+        per = cpu_images_per_worker(cores)
         rate, dt = cpu_preprocess_rate(per, cores)
         import PIL
 
@@ -388,7 +402,8 @@ def main():
                        "path": "fused" if info["fused_images"] == n else ("two-pass" if info["fused_images"] == 0 else "mixed"),
                        "parity_spot_check": parity},
             "roofline": {"bound": "hbm", "achieved": algo / kern_s / 1e9, "peak": peak, "unit": "GB/s",
-                         "frac": algo / kern_s / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": algo / kern_s / 1e9 / peak, "traffic": ncu_traffic("k_preprocess_fused_cfg3"),
+                         "peak_source": peak_src,
                          "kernel": "all kernels of one step (%d launch(es)/step)" % (launches // max(args.steps, 1)),
                          "algorithmic_bytes_per_launch": algo},
             "cpu_baseline": cpu,

@@ -128,7 +128,13 @@ __device__ __forceinline__ int clamp_u64_to(unsigned long long v, int hi) {
 }
 // Word whose lanes selected by `mask` are needed. Aligned case: one 32-bit load (never crosses a
 // page). Misaligned case: only the needed bytes are touched.
-__device__ __forceinline__ uint32_t load_word(const uint8_t* p, bool word_ok, uint32_t mask = 0xffffffffu) {
+__device__ __forceinline__ uint32_t load_word(const uint8_t* p, bool word_ok, uint32_t mask = 0xffffffffu,
+                                              bool in_smem = false) {
+  if (in_smem) {  // p points into this thread's shared-memory slot (always word aligned)
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(p))));
+    return v;
+  }
   if (word_ok) return ldg_u32(p);
   uint32_t v = 0;
 #pragma unroll
@@ -147,7 +153,7 @@ __device__ __forceinline__ uint32_t load_word(const uint8_t* p, bool word_ok, ui
 template <bool TO_STREAM, bool WORD_OK>
 __device__ __forceinline__ uint32_t compose_word(const unsigned long long* s_off, int nE, int e,
                                                  unsigned long long rel, unsigned long long e0,
-                                                 const uint8_t* sp) {
+                                                 const uint8_t* sp, bool in_smem = false) {
   if (TO_STREAM) {
     const unsigned long long st = elem_start<true>(s_off, e);
     const unsigned long long len = s_off[e + 1] - s_off[e];
@@ -157,7 +163,7 @@ __device__ __forceinline__ uint32_t compose_word(const unsigned long long* s_off
     uint32_t w = 0;
     if (r < 4) w = shr_bytes((uint32_t)len, r) & bytemask(n1);
     const uint32_t pm = bytemask(n2) & ~bytemask(n1);
-    if (pm) w |= load_word(sp - 4ull * (e0 + e + 1), WORD_OK, pm) & pm;
+    if (pm) w |= load_word(sp - 4ull * (e0 + e + 1), WORD_OK, pm, in_smem) & pm;
     if (n2 < 4 && e + 1 < nE) w |= shl_bytes((uint32_t)(s_off[e + 2] - s_off[e + 1]), n2);
     return w;
   } else {
@@ -168,7 +174,7 @@ __device__ __forceinline__ uint32_t compose_word(const unsigned long long* s_off
       const int n = clamp_u64_to(en - rel, 4);  // lanes [lane, n) come from element e
       if (n > lane) {
         const uint32_t m = bytemask(n) & ~bytemask(lane);
-        w |= load_word(sp + 4ull * (e0 + e + 1), WORD_OK, m) & m;
+        w |= load_word(sp + 4ull * (e0 + e + 1), WORD_OK, m, in_smem) & m;
         lane = n;
       }
       if (lane < 4) e++;
@@ -179,15 +185,58 @@ __device__ __forceinline__ uint32_t compose_word(const unsigned long long* s_off
 
 // Builds one boundary chunk (16 aligned output bytes, of which [A, lim) belong to this tile) and
 // stores it. `e` is an element at or before the one that holds the chunk's first in-range byte.
+// The source bytes a boundary chunk needs sit in one or two 32-byte sectors; they are fetched once,
+// as up to three aligned 16-byte loads into a per-thread shared-memory slot, and the words are then
+// composed from the slot. (Composing straight from global memory issued ~10 separate sector
+// accesses per chunk and tripled the L2 -> L1 traffic of the whole kernel.)
+constexpr int kSlotBytes = 48;
+
 template <bool TO_STREAM, bool WORD_OK>
 __device__ __forceinline__ void assemble_chunk(const unsigned long long* s_off, int nE, unsigned long long A,
                                                unsigned long long lim, unsigned long long e0, int e,
                                                unsigned long long q, unsigned long long mis,
-                                               const uint8_t* __restrict__ src, uint8_t* __restrict__ vd) {
+                                               const uint8_t* __restrict__ src, uint8_t* __restrict__ vd,
+                                               uint8_t* slot) {
   const unsigned long long cb = q << 4;
   const unsigned long long a = max(cb, A), b = min(cb + 16, lim);
   if (a >= b) return;
   const bool full = (a == cb) && (b == cb + 16);
+  // element of the first in-range byte, and of the last one
+  while (e + 1 < nE && elem_start<TO_STREAM>(s_off, e + 1) <= a - A) e++;
+  int eb = e;
+  while (eb + 1 < nE && elem_start<TO_STREAM>(s_off, eb + 1) <= b - 1 - A) eb++;
+  // source offsets (relative to src) that can be touched: [lo_off, hi_off)
+  const uint8_t* sb = src;  // sb[x] = source byte at offset x
+  bool staged = false;
+  if (WORD_OK) {
+    // exact range of source bytes this chunk needs, widened to whole aligned words (compose_word
+    // loads aligned words); every 16-byte block fetched below therefore holds a needed byte
+    long long lo_off, hi_off;
+    if (TO_STREAM) {
+      const unsigned long long blob0 = A - mis - 4ull * e0;  // blob offset of the tile's first element
+      const unsigned long long ra = a - A, rb = b - 1 - A;
+      lo_off = ra < elem_start<true>(s_off, e) + 4 ? (long long)(blob0 + s_off[e])
+                                                    : (long long)(a - mis) - 4ll * (long long)(e0 + e + 1);
+      hi_off = rb < elem_start<true>(s_off, eb) + 4 ? (long long)(blob0 + s_off[eb])
+                                                     : (long long)(b - mis) - 4ll * (long long)(e0 + eb + 1);
+    } else {
+      lo_off = (long long)(a - mis) + 4ll * (long long)(e0 + e + 1);
+      hi_off = (long long)(b - mis) + 4ll * (long long)(e0 + eb + 1);
+    }
+    lo_off &= ~3ll;
+    hi_off = (hi_off + 3) & ~3ll;
+    if (lo_off < 0) lo_off = 0;
+    const long long base = lo_off & ~15ll;
+    if (hi_off > lo_off && hi_off - base <= kSlotBytes &&
+        ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+      uint4* s4 = reinterpret_cast<uint4*>(slot);
+#pragma unroll
+      for (int k = 0; k < kSlotBytes / 16; k++)
+        if (base + 16 * k < hi_off) s4[k] = __ldg(reinterpret_cast<const uint4*>(src + base) + k);
+      sb = slot - base;  // only this thread touches its slot: no barrier needed
+      staged = true;
+    }
+  }
   uint32_t w[4];
 #pragma unroll
   for (int wi = 0; wi < 4; wi++) {
@@ -199,7 +248,7 @@ __device__ __forceinline__ void assemble_chunk(const unsigned long long* s_off, 
     const unsigned long long rel = wa >= A ? wa - A : 0;
     while (e + 1 < nE && elem_start<TO_STREAM>(s_off, e + 1) <= rel) e++;
     if (wa >= A) {
-      w[wi] = compose_word<TO_STREAM, WORD_OK>(s_off, nE, e, rel, e0, src + (wa - mis));
+      w[wi] = compose_word<TO_STREAM, WORD_OK>(s_off, nE, e, rel, e0, sb + (wa - mis), staged);
     } else {
       // word straddles the tile start: only lanes >= A - wa are ours; compose them byte-wise
       uint32_t v = 0;
@@ -231,7 +280,7 @@ template <bool TO_STREAM, bool WORD_OK>
 __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int nE,
                                           unsigned long long blob0, unsigned long long e0,
                                           const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
-                                          unsigned long long dst_capacity, unsigned short* s_tab) {
+                                          unsigned long long dst_capacity, unsigned short* s_tab, uint8_t* slot) {
   // output coordinates are shifted by `mis` so that multiples of 16 are 16-byte aligned addresses
   const unsigned long long mis = reinterpret_cast<uintptr_t>(dst) & 15;
   uint8_t* vd = dst - mis;
@@ -305,12 +354,12 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
           const unsigned long long hp = A + elem_start<true>(s_off, e - 1);
           own_a = ((hp + 3) >> 4) != qa;  // the previous prefix does not reach into qa
         }
-        if (own_a) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, qa, mis, src, vd);
-        if (qb != qa) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e, qb, mis, src, vd);
+        if (own_a) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, qa, mis, src, vd, slot);
+        if (qb != qa) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e, qb, mis, src, vd, slot);
       } else if (lim & 15) {  // partial tail chunk with no prefix of this tile in it
         const unsigned long long qt = lim >> 4;
         const unsigned long long hl = A + elem_start<true>(s_off, nE - 1);
-        if (((hl + 3) >> 4) < qt) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, nE - 1, qt, mis, src, vd);
+        if (((hl + 3) >> 4) < qt) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, nE - 1, qt, mis, src, vd, slot);
       }
     } else {
       // boundary point of pseudo-element e: its start (e < nE) or the tile end (e == nE)
@@ -323,7 +372,7 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
         own = (bp >> 4) < q || (bp & 15) == 0;  // previous boundary is not strictly inside chunk q
         if ((bp >> 4) == q && (bp & 15) == 0) own = true;
       }
-      if (own) assemble_chunk<false, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, q, mis, src, vd);
+      if (own) assemble_chunk<false, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, q, mis, src, vd, slot);
     }
   }
 }
@@ -341,6 +390,7 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
   __shared__ unsigned long long s_prefix;
   __shared__ unsigned int s_tile;
   __shared__ unsigned short s_tab[kTabSize + 1];
+  __shared__ __align__(16) uint8_t s_slots[kSerThreads * kSlotBytes];
   unsigned long long* status = ws + WS_HEADER_WORDS;
   if (threadIdx.x == 0) s_tile = atomicAdd(reinterpret_cast<unsigned int*>(&ws[WS_TICKET]), 1u);
   __syncthreads();
@@ -422,7 +472,7 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
                             : payload[(e0 + lo) * (unsigned long long)width + (rel - es - 4)];
     }
   } else {
-    move_tile<true, WORD_OK>(s_off, nE, blob0, e0, payload, dst, dst_capacity, s_tab);
+    move_tile<true, WORD_OK>(s_off, nE, blob0, e0, payload, dst, dst_capacity, s_tab, s_slots + threadIdx.x * kSlotBytes);
   }
 }
 
@@ -741,6 +791,7 @@ k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ o
              unsigned long long blob_capacity) {
   __shared__ unsigned long long s_off[kGatTile + 1];
   __shared__ unsigned short s_tab[kTabSize + 1];
+  __shared__ __align__(16) uint8_t s_slots[kGatThreads * kSlotBytes];
   const unsigned long long N = hdr[DW_NELEM];
   if (hdr[DW_STATUS] != 0) return;
   const unsigned long long e0 = (unsigned long long)blockIdx.x * kGatTile;
@@ -750,7 +801,7 @@ k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ o
   for (int i = threadIdx.x; i <= nE; i += kGatThreads)
     s_off[i] = (unsigned long long)offsets[e0 + i] - b0;
   __syncthreads();
-  move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity, s_tab);
+  move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity, s_tab, s_slots + threadIdx.x * kSlotBytes);
 }
 
 static uint64_t des_chunks(uint64_t stream_bytes) { return (stream_bytes + kDesChunk - 1) / kDesChunk; }
