@@ -192,3 +192,43 @@ def test_serialize_into_region_and_capacity_error():
         assert ei.value.code == _lib.TCB_ERR_OUT_OF_RANGE
     finally:
         cudashm.destroy_shared_memory_region(region)
+
+
+def test_full_size_cfg4_roundtrip_16m_strings():
+    """cfg4 at full size: 16M strings of 0..256 bytes (~2.1 GB stream) generated and serialised on
+    the device, then decoded from a CUDA shared-memory region. Size-independent properties:
+    decode(serialize(x)) == x for lengths and payload, offsets are non-decreasing and end at the
+    payload size, a limited decode returns a prefix, and the stream length equals P + 4N."""
+    import torch
+
+    from triton_client_b200 import utils as u
+    from triton_client_b200.utils import cuda_shared_memory as cudashm
+
+    N = 16_000_000
+    g = torch.Generator(device="cuda").manual_seed(43)
+    lens = torch.randint(0, 257, (N,), dtype=torch.int32, device="cuda", generator=g)
+    P = int(lens.sum(dtype=torch.int64).item())
+    blob = torch.randint(0, 256, (P,), dtype=torch.uint8, device="cuda", generator=g)
+    region = cudashm.create_shared_memory_region("cfg4", P + 4 * N, 0)
+    try:
+        _, total = u.serialize_to_device(blob, lens, out=region)
+        assert total == P + 4 * N
+        offsets, payload = u.deserialize_from_device(region, total)
+        assert offsets.numel() == N + 1 and payload.numel() == P
+        assert torch.equal(offsets[1:] - offsets[:-1], lens.to(torch.int64))
+        assert int(offsets[0]) == 0 and int(offsets[-1]) == P
+        assert torch.equal(payload, blob)
+        m = 1_234_567
+        off2, pay2 = u.deserialize_from_device(region, None, max_elements=m)
+        assert off2.numel() == m + 1 and torch.equal(off2, offsets[: m + 1])
+        assert torch.equal(pay2, blob[: int(off2[-1])])
+        # a strided sample of elements through the reference-facing API
+        h = cudashm.get_contents_as_numpy(region, np.object_, [1000])
+        lh = lens[:1000].cpu().numpy()
+        bh = blob[: int(lh.sum())].cpu().numpy().tobytes()
+        pos = 0
+        for i in range(1000):
+            assert h[i] == bh[pos: pos + lh[i]]
+            pos += int(lh[i])
+    finally:
+        cudashm.destroy_shared_memory_region(region)

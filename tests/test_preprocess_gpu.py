@@ -239,3 +239,57 @@ def test_unaligned_and_pitched_sources():
     ref = oracle_preprocess(wide[:, : 640 * 3].reshape(480, 640, 3), 3, 224, 224, 2, "FP32", "VGG")
     assert np.array_equal(out.cpu().numpy().view(np.float32).reshape(3, 224, 224), ref)
     plan.close()
+
+
+def test_full_size_properties_cfg5_mixed_resolution():
+    """cfg5 at full size: 8192 mixed-resolution images (SURVEY.md 8d size menu, drawn with
+    default_rng(1234).choice) -> 224x224 fp16 NHWC INCEPTION in one region. Checked through
+    size-independent properties: duplicated sources give identical outputs, constant images map to
+    the table constant, identity-size images equal the table applied to the source, and one image
+    per size class equals the oracle."""
+    import torch
+
+    from triton_client_b200.image_client import PreprocessPlan
+    from triton_client_b200.utils import cuda_shared_memory as cudashm
+
+    menu = [(640, 480), (800, 600), (1024, 768), (1280, 720), (1920, 1080), (500, 375), (375, 500), (224, 224), (150, 100)]
+    n = 8192
+    pick = np.random.default_rng(1234).choice(len(menu), size=n)
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    pools, cursor = [], [0] * len(menu)
+    for ci, (W, H) in enumerate(menu):
+        cnt = int((pick == ci).sum())
+        pools.append(torch.randint(0, 256, (max(cnt, 1), H, W, 3), dtype=torch.uint8, device="cuda", generator=g))
+    pools[4][3] = pools[4][1]        # two identical 1080p sources
+    pools[0][2] = 255                # constant images
+    pools[2][2] = 0
+    sizes, ptrs, where = [], [], []
+    for i in range(n):
+        ci = int(pick[i])
+        W, H = menu[ci]
+        sizes.append((W, H, 3))
+        ptrs.append(pools[ci][cursor[ci]].data_ptr())
+        where.append((ci, cursor[ci]))
+        cursor[ci] += 1
+    plan = PreprocessPlan(sizes, 1, "FP16", 3, 224, 224, "INCEPTION", device=0)
+    nbytes = n * plan.out_bytes_per_image
+    region = cudashm.create_shared_memory_region("cfg5", nbytes, 0)
+    try:
+        plan.run(ptrs, region._base_addr, nbytes)
+        torch.cuda.synchronize()
+        out = torch.from_dlpack(cudashm.as_shared_memory_tensor(region, "FP16", [n, 224, 224, 3]))
+        idx = {w: i for i, w in enumerate(where)}
+        assert torch.equal(out[idx[(4, 3)]], out[idx[(4, 1)]])
+        lut = pb.scaling_lut("FP16", 3, "INCEPTION")
+        assert torch.all(out[idx[(0, 2)]] == float(lut[0, 255]))
+        assert torch.all(out[idx[(2, 2)]] == float(lut[0, 0]))
+        for ci in range(len(menu)):            # one image per size class against the oracle
+            i = idx[(ci, 0)]
+            ref = oracle_preprocess(pools[ci][0].cpu().numpy(), 3, 224, 224, 1, "FP16", "INCEPTION")
+            assert np.array_equal(out[i].cpu().numpy(), ref), menu[ci]
+        info = plan.info()
+        assert info["fused_images"] == int((pick != 7).sum())   # everything but the identity-size class
+        del out
+    finally:
+        plan.close()
+        cudashm.destroy_shared_memory_region(region)
