@@ -20,8 +20,10 @@ def available():
 
 
 def reference_utils():
+    # appended, not prepended: the reference tree has its own top-level `tests` package, which must
+    # not shadow this repo's (spawned gloo ranks re-import tests.* with the parent's sys.path)
     if _LIB not in sys.path:
-        sys.path.insert(0, _LIB)
+        sys.path.append(_LIB)
     import tritonclient.utils as u  # noqa
     return u
 

@@ -70,9 +70,12 @@ def _worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
-def test_two_rank_gloo_sharded_bytes(tmp_path):
+def test_two_rank_gloo_sharded_bytes(tmp_path, monkeypatch):
     world = 2
     port = _free_port()
+    # spawned ranks must be able to import this module (tests.*) whatever pytest's cwd / import mode
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    monkeypatch.setenv("PYTHONPATH", root + os.pathsep + os.environ.get("PYTHONPATH", ""))
     mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
     blob, lens = cases.gbytes(1000)
     whole = bc.serialize_elements(cases.to_object_array(blob, lens))
