@@ -232,3 +232,43 @@ def test_full_size_cfg4_roundtrip_16m_strings():
             pos += int(lh[i])
     finally:
         cudashm.destroy_shared_memory_region(region)
+
+
+@pytest.mark.parametrize("case", ["mixed", "short", "long", "empties", "one_chunk", "chunk_edge"])
+def test_decode_limits_garbage_tails_and_chunk_edges(case):
+    """Offsets and payload must equal the oracle's for unlimited decodes, for limited decodes at
+    every interesting cut, and with garbage after the requested elements (a region larger than
+    its contents, as get_contents_as_numpy sees it); truncation must raise struct.error."""
+    import torch
+
+    from triton_client_b200 import utils as u
+
+    rng = np.random.default_rng(11)
+    lens = {
+        "mixed": rng.integers(0, 257, 30000),
+        "short": rng.integers(0, 6, 60000),
+        "long": rng.integers(3000, 40000, 60),
+        "empties": np.zeros(9000, dtype=np.int64),
+        "one_chunk": rng.integers(0, 100, 50),
+        # elements that end exactly on / one byte around the 16 KiB chunk boundaries
+        "chunk_edge": np.array([16380, 16380, 16379, 1, 16376, 16385, 0, 16371, 4, 32764, 5], dtype=np.int64),
+    }[case].astype(np.int64)
+    total = int(lens.sum())
+    blob = rng.integers(0, 256, total, dtype=np.uint8)
+    ref = clib.bytes_serialize(blob, lens)
+    ref_off = np.concatenate([[0], np.cumsum(lens)])
+    tail = rng.integers(0, 256, 50000, dtype=np.uint8)
+    for garbage in (None, "random", "zeros"):
+        h = ref if garbage is None else np.concatenate([ref, tail if garbage == "random" else np.zeros_like(tail)])
+        out = torch.from_numpy(h).cuda()
+        cuts = [len(lens)] if garbage else [-1, len(lens)]
+        cuts += [1, len(lens) // 2, len(lens) - 1]
+        for m in cuts:
+            oa, pa = u.deserialize_from_device(out, h.size, max_elements=m)
+            n = len(lens) if m < 0 else m
+            assert np.array_equal(oa.cpu().numpy(), ref_off[: n + 1]), (case, garbage, m)
+            assert np.array_equal(pa.cpu().numpy(), blob[: ref_off[n]]), (case, garbage, m)
+    out = torch.from_numpy(ref).cuda()
+    for kw in ({"nbytes": ref.size - 1}, {"nbytes": ref.size, "max_elements": len(lens) + 1}):
+        with pytest.raises(struct.error):
+            u.deserialize_from_device(out, kw["nbytes"], max_elements=kw.get("max_elements", -1))

@@ -276,6 +276,65 @@ __device__ __forceinline__ void assemble_chunk(const unsigned long long* s_off, 
   }
 }
 
+// Fast paths of phase B (word-aligned copies only). The common boundary chunk holds exactly one
+// boundary: the tail of element e-1, (serialise: the length prefix of e,) the head of element e,
+// and both payloads reach the chunk's edges. Its 16 bytes then come from five consecutive aligned
+// source words (the two elements' source positions differ by exactly one word) merged with byte
+// masks: no search, no per-byte work. Returns false when the chunk is not of that shape.
+template <bool WORD_OK>
+__device__ __forceinline__ bool fast_prefix_chunk(const unsigned long long* s_off, int nE, int e,
+                                                  unsigned long long hs, unsigned long long cb,
+                                                  unsigned long long A, unsigned long long lim,
+                                                  unsigned long long e0, unsigned long long mis,
+                                                  const uint8_t* __restrict__ src, uint8_t* __restrict__ vd) {
+  if (!WORD_OK || e == 0 || cb < A || cb + 16 > lim) return false;
+  if (hs > cb && A + elem_start<true>(s_off, e - 1) + 4 > cb) return false;   // e-1's payload must cover [cb, hs)
+  if (A + elem_start<true>(s_off, e + 1) < cb + 16) return false;             // e's payload must reach the chunk end
+  const uint32_t len = (uint32_t)(s_off[e + 1] - s_off[e]);
+  const int k = (int)(long long)(hs - cb);                                    // prefix position in the chunk, -3..15
+  const uint8_t* B = src + (cb - mis) - 4ull * (e0 + e + 1);                  // source of chunk byte 0 as payload of e
+  uint32_t P[5];
+#pragma unroll
+  for (int j = 0; j < 5; j++) {
+    // word j is payload of e for output word j, and payload of e-1 for output word j-1
+    const bool need = (j < 4 && 4 * j + 3 >= k + 4) || (j >= 1 && 4 * (j - 1) < k);
+    P[j] = need ? ldg_u32(B + 4 * j) : 0u;
+  }
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int t = k - 4 * i;  // prefix start relative to this word
+    const uint32_t mA = bytemask(t), mB = bytemask(t + 4);
+    const uint32_t ls = t >= 0 ? shl_bytes(len, t) : shr_bytes(len, -t);
+    w[i] = (P[i + 1] & mA) | (ls & mB & ~mA) | (P[i] & ~mB);
+  }
+  st_v4(vd + cb, w[0], w[1], w[2], w[3]);
+  return true;
+}
+
+template <bool WORD_OK>
+__device__ __forceinline__ bool fast_boundary_chunk(const unsigned long long* s_off, int nE, int e,
+                                                    unsigned long long be, unsigned long long cb,
+                                                    unsigned long long A, unsigned long long lim,
+                                                    unsigned long long e0, unsigned long long mis,
+                                                    const uint8_t* __restrict__ src, uint8_t* __restrict__ vd) {
+  if (!WORD_OK || e == 0 || e >= nE || cb < A || cb + 16 > lim) return false;
+  if (A + s_off[e - 1] > cb || A + s_off[e + 1] < cb + 16) return false;  // exactly one boundary inside the chunk
+  const int k = (int)(be - cb);                                           // 1..15
+  const uint8_t* S = src + (cb - mis) + 4ull * (e0 + e);                  // source of chunk byte 0 as payload of e-1
+  uint32_t W[5];
+#pragma unroll
+  for (int j = 0; j < 5; j++) W[j] = ldg_u32(S + 4 * j);  // [S, S+20) lies between two payload bytes that exist
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const uint32_t m = bytemask(k - 4 * i);
+    w[i] = (W[i] & m) | (W[i + 1] & ~m);
+  }
+  st_v4(vd + cb, w[0], w[1], w[2], w[3]);
+  return true;
+}
+
 template <bool TO_STREAM, bool WORD_OK>
 __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int nE,
                                           unsigned long long blob0, unsigned long long e0,
@@ -303,8 +362,8 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
   __syncthreads();
   // ---- phase A: interior chunks, two per thread in flight ------------------------------------------------
   const unsigned long long q0 = (A + 15) >> 4, q1 = lim >> 4;  // chunks fully inside [A, lim)
-  auto locate = [&](unsigned long long q, const uint8_t*& sp) -> bool {  // interior? -> source pointer
-    if (q >= q1) return false;
+  auto locate = [&](unsigned long long q, unsigned long long qlim, const uint8_t*& sp) -> bool {  // interior? -> source pointer
+    if (q >= qlim) return false;
     const unsigned long long cb = q << 4;
     const unsigned long long rel = cb - A;
     int e = s_tab[rel >> tsh];
@@ -320,14 +379,21 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
     return true;
   };
   constexpr int kFly = 4;  // chunks in flight per thread: all loads are issued before the first store
-  for (unsigned long long q = q0 + threadIdx.x; q < q1; q += (unsigned long long)kFly * blockDim.x) {
+  // The tile is walked in sub-tiles of blockDim.x elements, phase A then phase B for each: phase B
+  // re-reads sectors that phase A touched, and with both phases run over the whole 1024-element
+  // tile (~136 KB in, ~136 KB out, x 592 resident CTAs > L2) those re-reads all missed L2.
+  for (int sub = 0; sub <= nE; sub += blockDim.x) {
+  const int sub_end = min(sub + (int)blockDim.x, nE);
+  const unsigned long long qs0 = sub == 0 ? q0 : max(q0, (A + elem_start<TO_STREAM>(s_off, sub) + 15) >> 4);
+  const unsigned long long qs1 = sub_end == nE ? q1 : min(q1, (A + elem_start<TO_STREAM>(s_off, sub_end)) >> 4);
+  for (unsigned long long q = qs0 + threadIdx.x; q < qs1; q += (unsigned long long)kFly * blockDim.x) {
     const uint8_t* sp[kFly];
     bool ok[kFly];
     uint32_t w[kFly][4];
 #pragma unroll
     for (int f = 0; f < kFly; f++) {
       sp[f] = src;
-      ok[f] = locate(q + (unsigned long long)f * blockDim.x, sp[f]);
+      ok[f] = locate(q + (unsigned long long)f * blockDim.x, qs1, sp[f]);
     }
 #pragma unroll
     for (int f = 0; f < kFly; f++) {
@@ -344,7 +410,9 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
   // Boundary points b_e: for TO_STREAM the prefix bytes [hs_e, hs_e + 4) of every element; otherwise
   // the element start offsets. Chunk q is owned by the first element whose boundary touches it; the
   // tile's head (A) and tail (lim) are the boundaries of pseudo-elements 0 and nE.
-  for (int e = threadIdx.x; e <= nE; e += blockDim.x) {
+  {
+    const int e = sub + threadIdx.x;
+    if (e > nE) continue;
     if (TO_STREAM) {
       if (e < nE) {
         const unsigned long long hs = A + elem_start<true>(s_off, e);
@@ -354,8 +422,10 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
           const unsigned long long hp = A + elem_start<true>(s_off, e - 1);
           own_a = ((hp + 3) >> 4) != qa;  // the previous prefix does not reach into qa
         }
-        if (own_a) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, qa, mis, src, vd, slot);
-        if (qb != qa) assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e, qb, mis, src, vd, slot);
+        if (own_a && !fast_prefix_chunk<WORD_OK>(s_off, nE, e, hs, qa << 4, A, lim, e0, mis, src, vd))
+          assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, qa, mis, src, vd, slot);
+        if (qb != qa && !fast_prefix_chunk<WORD_OK>(s_off, nE, e, hs, qb << 4, A, lim, e0, mis, src, vd))
+          assemble_chunk<true, WORD_OK>(s_off, nE, A, lim, e0, e, qb, mis, src, vd, slot);
       } else if (lim & 15) {  // partial tail chunk with no prefix of this tile in it
         const unsigned long long qt = lim >> 4;
         const unsigned long long hl = A + elem_start<true>(s_off, nE - 1);
@@ -372,9 +442,11 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
         own = (bp >> 4) < q || (bp & 15) == 0;  // previous boundary is not strictly inside chunk q
         if ((bp >> 4) == q && (bp & 15) == 0) own = true;
       }
-      if (own) assemble_chunk<false, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, q, mis, src, vd, slot);
+      if (own && !fast_boundary_chunk<WORD_OK>(s_off, nE, e, be, q << 4, A, lim, e0, mis, src, vd))
+        assemble_chunk<false, WORD_OK>(s_off, nE, A, lim, e0, e > 0 ? e - 1 : 0, q, mis, src, vd, slot);
     }
   }
+  }  // sub-tiles
 }
 
 // LEN_SIZE: 4 or 8 bytes per length; FIXED: lengths come from fixed-width rows (trailing NULs
