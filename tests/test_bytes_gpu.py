@@ -272,3 +272,33 @@ def test_decode_limits_garbage_tails_and_chunk_edges(case):
     for kw in ({"nbytes": ref.size - 1}, {"nbytes": ref.size, "max_elements": len(lens) + 1}):
         with pytest.raises(struct.error):
             u.deserialize_from_device(out, kw["nbytes"], max_elements=kw.get("max_elements", -1))
+
+
+def test_tile_larger_than_2gib_takes_the_64bit_copy():
+    """One tile of 1024 elements whose output exceeds 2^31 bytes: the copy falls back from 32-bit
+    tile-relative offsets to 64-bit ones. Checked on the device slice by slice (header words at
+    their known positions, payload slices equal to the blob) and by the round trip."""
+    import torch
+
+    from triton_client_b200 import utils as u
+
+    big = (1 << 30) + (1 << 28) + 3
+    lens_h = np.array([big, 5, big - 1, 0, 7, 13], dtype=np.int64)
+    lens = torch.from_numpy(lens_h).cuda()
+    P = int(lens_h.sum())
+    g = torch.Generator(device="cuda").manual_seed(5)
+    blob = torch.randint(0, 256, (P,), dtype=torch.uint8, device="cuda", generator=g)
+    out, total = u.serialize_to_device(blob, lens)
+    assert total == P + 4 * len(lens_h)
+    pos = 0
+    src = 0
+    for n in lens_h:
+        n = int(n)
+        hdr = out[pos: pos + 4].cpu().numpy().tobytes()
+        assert struct.unpack("<I", hdr)[0] == n
+        assert torch.equal(out[pos + 4: pos + 4 + n], blob[src: src + n])
+        pos += 4 + n
+        src += n
+    offsets, payload = u.deserialize_from_device(out, total)
+    assert np.array_equal(np.diff(offsets.cpu().numpy()), lens_h)
+    assert torch.equal(payload, blob)

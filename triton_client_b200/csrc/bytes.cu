@@ -449,6 +449,177 @@ __device__ __forceinline__ void move_tile(const unsigned long long* s_off, int n
   }  // sub-tiles
 }
 
+constexpr unsigned long long kTile32Limit = (1ull << 31) - 64;  // tile output bytes the 32-bit variant handles
+
+// ---- 32-bit variant of move_tile ---------------------------------------------------------------
+// Same algorithm, but every position is a 32-bit offset from the 16-byte aligned start T of the
+// tile's output, element starts come from a precomputed table s_st[] (serialise: start of the
+// length prefix, deserialise: start of the payload) and the source is addressed as srcT + offset.
+// The 64-bit version spent most of its instructions on 64-bit address arithmetic and on
+// recomputing s_off[e] + 4*e. Caller guarantees that the tile's output is shorter than 2^31 bytes.
+template <bool WORD_OK>
+__device__ __forceinline__ bool fast_prefix_chunk32(const uint32_t* s_st, int e, uint32_t hs, uint32_t cb,
+                                                    uint32_t a, uint32_t lm, const uint8_t* __restrict__ srcT,
+                                                    uint8_t* __restrict__ vdT) {
+  if (!WORD_OK || e == 0 || cb < a || cb + 16 > lm) return false;
+  if (hs > cb && s_st[e - 1] + 4 > cb) return false;  // e-1's payload must cover [cb, hs)
+  const uint32_t nx = s_st[e + 1];
+  if (nx < cb + 16) return false;                     // e's payload must reach the chunk end
+  const uint32_t len = nx - hs - 4;
+  const int k = (int)hs - (int)cb;                    // prefix position in the chunk, -3..15
+  const uint8_t* B = srcT + ((long long)(int)cb - 4ll * (e + 1));  // source of chunk byte 0 as payload of e
+  uint32_t P[5];
+#pragma unroll
+  for (int j = 0; j < 5; j++) {
+    const bool need = (j < 4 && 4 * j + 3 >= k + 4) || (j >= 1 && 4 * (j - 1) < k);
+    P[j] = need ? ldg_u32(B + 4 * j) : 0u;
+  }
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int t = k - 4 * i;
+    const uint32_t mA = bytemask(t), mB = bytemask(t + 4);
+    const uint32_t ls = t >= 0 ? shl_bytes(len, t) : shr_bytes(len, -t);
+    w[i] = (P[i + 1] & mA) | (ls & mB & ~mA) | (P[i] & ~mB);
+  }
+  st_v4(vdT + cb, w[0], w[1], w[2], w[3]);
+  return true;
+}
+
+template <bool WORD_OK>
+__device__ __forceinline__ bool fast_boundary_chunk32(const uint32_t* s_st, int nE, int e, uint32_t be, uint32_t cb,
+                                                      uint32_t a, uint32_t lm, const uint8_t* __restrict__ srcT,
+                                                      uint8_t* __restrict__ vdT) {
+  if (!WORD_OK || e == 0 || e >= nE || cb < a || cb + 16 > lm) return false;
+  if (s_st[e - 1] > cb || s_st[e + 1] < cb + 16) return false;  // exactly one boundary inside the chunk
+  const int k = (int)(be - cb);                                 // 1..15
+  const uint8_t* S = srcT + (cb + 4u * (uint32_t)e);            // source of chunk byte 0 as payload of e-1
+  uint32_t W[5];
+#pragma unroll
+  for (int j = 0; j < 5; j++) W[j] = ldg_u32(S + 4 * j);
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const uint32_t m = bytemask(k - 4 * i);
+    w[i] = (W[i] & m) | (W[i + 1] & ~m);
+  }
+  st_v4(vdT + cb, w[0], w[1], w[2], w[3]);
+  return true;
+}
+
+template <bool TO_STREAM, bool WORD_OK>
+__device__ __forceinline__ void move_tile32(const unsigned long long* s_off, uint32_t* s_st, int nE,
+                                            unsigned long long blob0, unsigned long long e0,
+                                            const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                            unsigned long long dst_capacity, unsigned short* s_tab, uint8_t* slot,
+                                            uint32_t* s_queue, unsigned int* s_qn) {
+  const unsigned long long mis = reinterpret_cast<uintptr_t>(dst) & 15;
+  uint8_t* vd = dst - mis;
+  const unsigned long long o0 = TO_STREAM ? blob0 + 4 * e0 : blob0;
+  const unsigned long long total = elem_start<TO_STREAM>(s_off, nE);
+  const unsigned long long lim = min(o0 + total, dst_capacity) + mis;
+  if (threadIdx.x == 0) *s_qn = 0;
+  const unsigned long long A = o0 + mis;
+  if (lim <= A) return;
+  const unsigned long long T = A & ~15ull;
+  const uint32_t a = (uint32_t)(A - T), lm = (uint32_t)(lim - T);
+  uint8_t* vdT = vd + T;
+  // source byte of output byte p (tile coordinates) of element e: srcT + p -/+ 4 * (e + 1)
+  const uint8_t* srcT = TO_STREAM ? src + (T - mis) - 4ull * e0 : src + (T - mis) + 4ull * e0;
+  int tsh = 8;
+  while (((a + (uint32_t)total) >> tsh) >= (uint32_t)kTabSize) tsh++;
+  for (int e = threadIdx.x; e <= nE; e += blockDim.x) {
+    const uint32_t s0 = a + (uint32_t)elem_start<TO_STREAM>(s_off, e);
+    s_st[e] = s0;
+    if (e < nE) {
+      const uint32_t s1 = a + (uint32_t)elem_start<TO_STREAM>(s_off, e + 1);
+      const uint32_t f0 = e == 0 ? 0u : s0;  // element 0 also answers for the bytes before the tile start
+      if (s1 > f0) {
+        const uint32_t t0 = (f0 + (1u << tsh) - 1) >> tsh, t1 = (s1 - 1) >> tsh;
+        for (uint32_t t = t0; t <= t1; t++) s_tab[t] = (unsigned short)e;
+      }
+    }
+  }
+  __syncthreads();
+  const uint32_t q0 = (a + 15) >> 4, q1 = lm >> 4;  // chunks fully inside the tile's output
+  const unsigned long long qT = T >> 4;
+  constexpr int kFly = 4;
+  for (int sub = 0; sub <= nE; sub += blockDim.x) {
+    const int sub_end = min(sub + (int)blockDim.x, nE);
+    const uint32_t qs0 = sub == 0 ? q0 : max(q0, (s_st[sub] + 15) >> 4);
+    const uint32_t qs1 = sub_end == nE ? q1 : min(q1, s_st[sub_end] >> 4);
+    // ---- phase A: chunks inside one payload --------------------------------------------------
+    for (uint32_t q = qs0 + threadIdx.x; q < qs1; q += kFly * blockDim.x) {
+      int so[kFly];
+      bool ok[kFly];
+      uint32_t w[kFly][4];
+#pragma unroll
+      for (int f = 0; f < kFly; f++) {
+        const uint32_t qq = q + f * blockDim.x;
+        ok[f] = false;
+        so[f] = 0;
+        if (qq < qs1) {
+          const uint32_t cb = qq << 4;
+          int e = s_tab[cb >> tsh];
+          uint32_t nx = s_st[e + 1];
+          while (nx <= cb) nx = s_st[++e + 1];
+          ok[f] = cb + 16 <= nx && (!TO_STREAM || cb >= s_st[e] + 4);
+          so[f] = TO_STREAM ? (int)cb - 4 * (e + 1) : (int)cb + 4 * (e + 1);
+        }
+      }
+#pragma unroll
+      for (int f = 0; f < kFly; f++) {
+        if (ok[f]) {
+          const uint8_t* sp = srcT + so[f];
+#pragma unroll
+          for (int k = 0; k < 4; k++) w[f][k] = load_word(sp + 4 * k, WORD_OK);
+        }
+      }
+#pragma unroll
+      for (int f = 0; f < kFly; f++)
+        if (ok[f]) st_v4(vdT + ((q + f * blockDim.x) << 4), w[f][0], w[f][1], w[f][2], w[f][3]);
+    }
+    // ---- phase B: boundary chunks of this sub-tile's elements ---------------------------------
+    const int e = sub + threadIdx.x;
+    if (e > nE) continue;
+    if (TO_STREAM) {
+      if (e < nE) {
+        const uint32_t hs = s_st[e];
+        const uint32_t qa = hs >> 4, qb = (hs + 3) >> 4;
+        const bool own_a = e == 0 || ((s_st[e - 1] + 3) >> 4) != qa;  // the previous prefix does not reach into qa
+        if (own_a && !fast_prefix_chunk32<WORD_OK>(s_st, e, hs, qa << 4, a, lm, srcT, vdT))
+          s_queue[atomicAdd(s_qn, 1u)] = qa;
+        if (qb != qa && !fast_prefix_chunk32<WORD_OK>(s_st, e, hs, qb << 4, a, lm, srcT, vdT))
+          s_queue[atomicAdd(s_qn, 1u)] = qb;
+      } else if (lm & 15) {  // partial tail chunk with no prefix of this tile in it
+        const uint32_t qt = lm >> 4;
+        if (((s_st[nE - 1] + 3) >> 4) < qt) s_queue[atomicAdd(s_qn, 1u)] = qt;
+      }
+    } else {
+      const uint32_t be = e < nE ? s_st[e] : lm;  // start of element e, or the tile end
+      if ((be & 15) == 0 || be > lm) continue;    // chunk-aligned boundaries create no boundary chunk
+      const uint32_t q = be >> 4;
+      bool own = true;
+      if (e > 0) {
+        const uint32_t bp = s_st[e - 1];
+        own = (bp >> 4) < q || (bp & 15) == 0;    // previous boundary is not strictly inside chunk q
+      }
+      if (own && !fast_boundary_chunk32<WORD_OK>(s_st, nE, e, be, q << 4, a, lm, srcT, vdT))
+        s_queue[atomicAdd(s_qn, 1u)] = q;
+    }
+  }
+  // ---- the boundary chunks that are not of the simple shape (several boundaries in 16 bytes, tile
+  // edges): queued above and assembled here by consecutive threads. Done in place, the general
+  // assembly ran with a handful of active lanes per warp in almost every warp.
+  __syncthreads();
+  const unsigned int nq = *s_qn;
+  for (unsigned int i = threadIdx.x; i < nq; i += blockDim.x) {
+    const uint32_t q = s_queue[i];
+    const int eh = s_tab[max(q << 4, a) >> tsh];  // an element at or before the chunk's first byte
+    assemble_chunk<TO_STREAM, WORD_OK>(s_off, nE, A, lim, e0, eh, qT + q, mis, src, vd, slot);
+  }
+}
+
 // LEN_SIZE: 4 or 8 bytes per length; FIXED: lengths come from fixed-width rows (trailing NULs
 // stripped) and the payload of element i starts at i * width instead of being packed.
 template <int LEN_SIZE, bool FIXED, bool WORD_OK>
@@ -458,6 +629,9 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
                   unsigned long long dst_capacity, unsigned long long* __restrict__ ws,
                   unsigned long long* __restrict__ total_out) {
   __shared__ unsigned long long s_off[kSerTile + 1];
+  __shared__ uint32_t s_st[kSerTile + 1];
+  __shared__ uint32_t s_queue[2 * kSerTile + 2];  // deferred boundary chunks (at most two per element + the tail)
+  __shared__ unsigned int s_qn;
   __shared__ unsigned long long s_warp[kSerThreads / 32];
   __shared__ unsigned long long s_prefix;
   __shared__ unsigned int s_tile;
@@ -544,7 +718,11 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
                             : payload[(e0 + lo) * (unsigned long long)width + (rel - es - 4)];
     }
   } else {
-    move_tile<true, WORD_OK>(s_off, nE, blob0, e0, payload, dst, dst_capacity, s_tab, s_slots + threadIdx.x * kSlotBytes);
+    uint8_t* slot = s_slots + threadIdx.x * kSlotBytes;
+    if (s_off[nE] + 4ull * nE < kTile32Limit)  // uniform across the CTA
+      move_tile32<true, WORD_OK>(s_off, s_st, nE, blob0, e0, payload, dst, dst_capacity, s_tab, slot, s_queue, &s_qn);
+    else
+      move_tile<true, WORD_OK>(s_off, nE, blob0, e0, payload, dst, dst_capacity, s_tab, slot);
   }
 }
 
@@ -862,6 +1040,9 @@ k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ o
              const unsigned long long* __restrict__ hdr, uint8_t* __restrict__ blob,
              unsigned long long blob_capacity) {
   __shared__ unsigned long long s_off[kGatTile + 1];
+  __shared__ uint32_t s_st[kGatTile + 1];
+  __shared__ uint32_t s_queue[kGatTile + 2];  // deferred boundary chunks (at most one per element + the tail)
+  __shared__ unsigned int s_qn;
   __shared__ unsigned short s_tab[kTabSize + 1];
   __shared__ __align__(16) uint8_t s_slots[kGatThreads * kSlotBytes];
   const unsigned long long N = hdr[DW_NELEM];
@@ -873,7 +1054,11 @@ k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ o
   for (int i = threadIdx.x; i <= nE; i += kGatThreads)
     s_off[i] = (unsigned long long)offsets[e0 + i] - b0;
   __syncthreads();
-  move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity, s_tab, s_slots + threadIdx.x * kSlotBytes);
+  uint8_t* slot = s_slots + threadIdx.x * kSlotBytes;
+  if (s_off[nE] < kTile32Limit)  // uniform across the CTA
+    move_tile32<false, WORD_OK>(s_off, s_st, nE, b0, e0, stream, blob, blob_capacity, s_tab, slot, s_queue, &s_qn);
+  else
+    move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity, s_tab, slot);
 }
 
 static uint64_t des_chunks(uint64_t stream_bytes) { return (stream_bytes + kDesChunk - 1) / kDesChunk; }
