@@ -97,7 +97,8 @@ struct FusedDesc {
   int32_t nwv;       // vertical coefficient words per output row
   int32_t hc_off;    // pool: packed H coefficients [out_w][nw][3]
   int32_t hw0_off;   // pool: first source word of every output column [out_w]
-  int32_t vc_off;    // pool: packed V coefficients [out_h][nwv][3]
+  int32_t hperm_off; // pool: output column of every thread [threads]
+  int32_t vc_off;    // pool: packed V coefficients [out_h][nwv][4] (k0, k1, k2, 0), 16-byte aligned
   int32_t vg_off;    // pool: (first group, last group) of every output row [out_h][2]
   int32_t vb_off;    // pool: Pillow bounds of the vertical axis [out_h][2]
   int32_t band_rows;
@@ -175,7 +176,7 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
 
   // ---- per-thread constants ------------------------------------------------------------------------
   const bool nchw = layout == TCB_LAYOUT_NCHW;
-  const int xx = tid;
+  const int xx = pool[d.hperm_off + tid];  // output column of this thread (>= out_w: none), see lane_columns()
   uint32_t kc[NW][3];
   int poff[NW];  // physical granule offsets of this column's NW source words
 #pragma unroll
@@ -300,10 +301,13 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
       }
     }
   }
-  auto vertical = [&](int yy) {
+  auto vertical = [&](int yy, int g_now, int slot_now) {
     const int gv0 = vg[2 * yy];
-    const int32_t* vc = pool + d.vc_off + (size_t)yy * d.nwv * 3;
-    const int slot0 = (gv0 - g_first) % ng;
+    const uint4* vc = reinterpret_cast<const uint4*>(pool + d.vc_off) + (size_t)yy * d.nwv;  // [nwv] x (k0, k1, k2, -)
+    // ring slot of the row's first group: the group being written now sits in slot_now and the row
+    // reaches back at most nwv = ng - 1 groups
+    int slot0 = slot_now - (g_now - gv0);
+    if (slot0 < 0) slot0 += ng;
     if (vec4) {
       if (tid < n_units) {  // first (normally only) unit of this thread: hoisted constants
         uint32_t a[4][3];
@@ -311,7 +315,8 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
         for (int v = 0; v < 4; v++) { a[v][0] = 1u << (kPrecisionBits - 1); a[v][1] = 0; a[v][2] = 0; }
         int slot = slot0;
         for (int j = 0; j < d.nwv; j++) {
-          const uint32_t k0 = __ldg(vc + 3 * j), k1 = __ldg(vc + 3 * j + 1), k2 = __ldg(vc + 3 * j + 2);
+          const uint4 kk = __ldg(vc + j);
+          const uint32_t k0 = kk.x, k1 = kk.y, k2 = kk.z;
           const uint4 px = *reinterpret_cast<const uint4*>(tmp4 + (size_t)slot * L + v_i0);
           a[0][0] = __dp4a(px.x, k0, a[0][0]); a[0][1] = __dp4a(px.x, k1, a[0][1]); a[0][2] = __dp4a(px.x, k2, a[0][2]);
           a[1][0] = __dp4a(px.y, k0, a[1][0]); a[1][1] = __dp4a(px.y, k1, a[1][1]); a[1][2] = __dp4a(px.y, k2, a[1][2]);
@@ -321,7 +326,7 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
         }
         uint32_t u[4];
 #pragma unroll
-        for (int v = 0; v < 4; v++) u[v] = min((a[v][0] + (a[v][1] << 8) + (a[v][2] << 16)) >> kPrecisionBits, 255u);
+        for (int v = 0; v < 4; v++) u[v] = (a[v][0] + (a[v][1] << 8) + (a[v][2] << 16)) >> kPrecisionBits;  // <= 255, see coeffs_never_clip
         const size_t e0 = v_e0 + (size_t)yy * v_erow;
         if (elem == 4) {
           const uint32_t* l32 = reinterpret_cast<const uint32_t*>(lut);
@@ -353,11 +358,11 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
           int slot = slot0;
           for (int j = 0; j < d.nwv; j++) {
             const uint32_t px = tmp4[(size_t)slot * L + iw];
-            a0 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j), a0); a1 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 1), a1);
-            a2 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 2), a2);
+            const uint4 kk = __ldg(vc + j);
+            a0 = __dp4a(px, kk.x, a0); a1 = __dp4a(px, kk.y, a1); a2 = __dp4a(px, kk.z, a2);
             if (++slot == ng) slot = 0;
           }
-          const uint32_t u = min((a0 + (a1 << 8) + (a2 << 16)) >> kPrecisionBits, 255u);
+          const uint32_t u = (a0 + (a1 << 8) + (a2 << 16)) >> kPrecisionBits;
           size_t e; int ch;
           if (nchw) { ch = iw / out_w; e = ((size_t)ch * out_h + yy) * out_w + (iw - ch * out_w); }
           else { ch = iw % C; e = (size_t)yy * L + iw; }
@@ -374,11 +379,11 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
         int slot = slot0;
         for (int j = 0; j < d.nwv; j++) {
           const uint32_t px = tmp4[(size_t)slot * L + i];
-          a0 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j), a0); a1 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 1), a1);
-          a2 = __dp4a(px, (uint32_t)__ldg(vc + 3 * j + 2), a2);
+          const uint4 kk = __ldg(vc + j);
+          a0 = __dp4a(px, kk.x, a0); a1 = __dp4a(px, kk.y, a1); a2 = __dp4a(px, kk.z, a2);
           if (++slot == ng) slot = 0;
         }
-        const uint32_t u = min((a0 + (a1 << 8) + (a2 << 16)) >> kPrecisionBits, 255u);
+        const uint32_t u = (a0 + (a1 << 8) + (a2 << 16)) >> kPrecisionBits;
         size_t e;
         int ch;
         if (nchw) { ch = i / out_w; e = ((size_t)ch * out_h + yy) * out_w + (i - ch * out_w); }
@@ -421,13 +426,13 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
           }
           uint32_t u[4];
 #pragma unroll
-          for (int r = 0; r < 4; r++) u[r] = min((a[r][0] + (a[r][1] << 8) + (a[r][2] << 16)) >> kPrecisionBits, 255u);
+          for (int r = 0; r < 4; r++) u[r] = (a[r][0] + (a[r][1] << 8) + (a[r][2] << 16)) >> kPrecisionBits;  // <= 255, see coeffs_never_clip
           out[ch * tmp_chs] = __byte_perm(__byte_perm(u[0], u[1], 0x0040), __byte_perm(u[2], u[3], 0x0040), 0x5410);
         }
       }
     }
     // vertical pass of the rows whose last group was written in an earlier phase
-    while (yy_next < yy1 && vg[2 * yy_next + 1] < g) vertical(yy_next++);
+    while (yy_next < yy1 && vg[2 * yy_next + 1] < g) vertical(yy_next++, g, slot);
     if (i < n_groups) {
       __syncthreads();  // P4 free again, tmp4 slot visible
       if (++slot == ng) slot = 0;
@@ -470,6 +475,81 @@ static int pack_axis(const std::vector<int32_t>& bounds, const std::vector<int32
   return nw;
 }
 
+// Pillow clips every pass to [0, 255]. With non-negative weights (BILINEAR) the clip never acts as
+// long as 2^21 + 255 * sum(k) < 2^30 for every output sample, i.e. sum(k) <= 2^22 + 8224; rounding
+// moves the sum by at most half a unit per tap. The fused kernel relies on this (no min/max in
+// the inner loops); a geometry that violates it takes the two-pass kernels.
+static bool coeffs_never_clip(const std::vector<int32_t>& bounds, const std::vector<int32_t>& kk, int ksize, int out) {
+  for (int o = 0; o < out; o++) {
+    long long sum = 0;
+    for (int t = 0; t < bounds[2 * o + 1]; t++) {
+      const int32_t k = kk[(size_t)o * ksize + t];
+      if (k < 0) return false;
+      sum += k;
+    }
+    if ((1ll << (kPrecisionBits - 1)) + 255ll * sum >= (1ll << 30)) return false;
+  }
+  return true;
+}
+
+// Which output column each thread of the CTA takes in the horizontal pass. Thread = column makes
+// consecutive lanes read P4 granules ~scale/4 apart (2.14 for 1080p -> 224), and the 8 lanes that
+// share one shared-memory wavefront of a 128-bit load then fall on 4-5 distinct 16-byte bank
+// groups: a 2-way conflict on the kernel's dominant shared-memory traffic. No padding or XOR
+// swizzle of P4 removes it (the stride is irregular), but the lane -> column map is free: group
+// the columns so that every quarter-warp holds 8 columns whose first granules differ mod 8 (all
+// NW loads shift them together). The better of this map and the identity is used.
+static double lds128_cost(const std::vector<int32_t>& first, const std::vector<int32_t>& perm, int out_w) {
+  long long waves = 0, n = 0;
+  for (size_t base = 0; base < perm.size(); base += 8) {
+    int cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::vector<int> seen;
+    int worst = 0;
+    for (size_t l = base; l < std::min(perm.size(), base + 8); l++) {
+      if (perm[l] >= out_w) continue;
+      const int g = first[perm[l]];
+      if (std::find(seen.begin(), seen.end(), g) != seen.end()) continue;  // same granule: broadcast
+      seen.push_back(g);
+      worst = std::max(worst, ++cnt[g & 7]);
+    }
+    if (worst) { waves += worst; n++; }
+  }
+  return n ? (double)waves / (double)n : 1.0;
+}
+
+static std::vector<int32_t> lane_columns(const std::vector<int32_t>& first, int out_w, int threads) {
+  std::vector<int32_t> ident(threads), perm;
+  for (int t = 0; t < threads; t++) ident[t] = std::min(t, out_w);
+  const int nq = (out_w + 7) / 8;
+  std::vector<std::vector<int>> quarters(nq), buckets(8);
+  std::vector<int> left;
+  for (int c = 0; c < out_w; c++) buckets[first[c] & 7].push_back(c);
+  for (auto& b : buckets)
+    for (size_t i = 0; i < b.size(); i++) {
+      if ((int)i < nq) quarters[i].push_back(b[i]); else left.push_back(b[i]);
+    }
+  for (auto& q : quarters) {
+    while (!left.empty() && q.size() < 8) {
+      size_t best = 0;
+      int best_cnt = 1 << 30;
+      for (size_t i = 0; i < left.size(); i++) {
+        int cnt = 0;
+        for (int x : q) cnt += (first[x] & 7) == (first[left[i]] & 7);
+        if (cnt < best_cnt) { best_cnt = cnt; best = i; }
+      }
+      q.push_back(left[best]);
+      left.erase(left.begin() + best);
+    }
+  }
+  for (auto& q : quarters) {
+    for (int c : q) perm.push_back(c);
+    for (size_t i = q.size(); i < 8; i++) perm.push_back(out_w);  // a short quarter: idle lanes
+  }
+  if (!left.empty() || (int)perm.size() > threads) return ident;  // does not fit the CTA: keep it simple
+  perm.resize(threads, out_w);
+  return lds128_cost(first, perm, out_w) < lds128_cost(first, ident, out_w) ? perm : ident;
+}
+
 static int nw_class(int nw) {
   for (int c : kNwClasses)
     if (nw <= c) return c;
@@ -490,10 +570,12 @@ static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc&
   if (out_w > kFusedMaxThreads) return false;
   std::vector<int32_t> b, k, packed, first;
   const int ksh = compute_axis_coeffs(d.W, out_w, b, k);
+  if (!coeffs_never_clip(b, k, ksh, out_w)) return false;
   const int nw = pack_axis(b, k, ksh, out_w, 0, packed, first);
   const int cls = nw_class(nw);
   if (cls < 0) return false;
   const int ksv = compute_axis_coeffs(d.H, out_h, b, k);
+  if (!coeffs_never_clip(b, k, ksv, out_h)) return false;
   const int nwv = pack_axis(b, k, ksv, out_h, 0, packed, first);
   if (nwv > 24) return false;
   g->nw_class = cls; g->nwv = nwv;
@@ -567,7 +649,7 @@ int fused_prepare(Plan& p) {
   FusedPlan* fp = new FusedPlan();
   fp->desc.resize(p.n);
   std::vector<int32_t> pool;
-  std::map<std::pair<int, int>, std::array<int32_t, 3>> htab;   // (W, class) -> hc_off, hw0_off, nw
+  std::map<std::pair<int, int>, std::array<int32_t, 3>> htab;   // (W, class) -> hc_off, hw0_off, hperm_off
   std::map<int, std::array<int32_t, 4>> vtab;                    // H -> vc_off, vg_off, vb_off, nwv
   auto align4 = [&]() { while (pool.size() % 4) pool.push_back(0); };
   for (int i = 0; i < p.n; i++) {
@@ -588,7 +670,8 @@ int fused_prepare(Plan& p) {
       std::array<int32_t, 3> e;
       align4(); e[0] = (int32_t)pool.size(); pool.insert(pool.end(), packed.begin(), packed.end());
       align4(); e[1] = (int32_t)pool.size(); pool.insert(pool.end(), first.begin(), first.end());
-      e[2] = g.nw_class;
+      const std::vector<int32_t> cols = lane_columns(first, p.out_w, g.threads);
+      align4(); e[2] = (int32_t)pool.size(); pool.insert(pool.end(), cols.begin(), cols.end());
       htab[hk] = e;
     }
     if (!vtab.count(d.H)) {
@@ -596,14 +679,17 @@ int fused_prepare(Plan& p) {
       const int ks = compute_axis_coeffs(d.H, p.out_h, b, k);
       const int nwv = pack_axis(b, k, ks, p.out_h, 0, packed, first, &last);
       std::array<int32_t, 4> e;
-      align4(); e[0] = (int32_t)pool.size(); pool.insert(pool.end(), packed.begin(), packed.end());
+      align4(); e[0] = (int32_t)pool.size();  // [out_h][nwv] x (k0, k1, k2, 0): one 128-bit load per tap word
+      for (size_t t = 0; t + 2 < packed.size(); t += 3) {
+        pool.push_back(packed[t]); pool.push_back(packed[t + 1]); pool.push_back(packed[t + 2]); pool.push_back(0);
+      }
       align4(); e[1] = (int32_t)pool.size();
       for (int o = 0; o < p.out_h; o++) { pool.push_back(first[o]); pool.push_back(last[o]); }
       align4(); e[2] = (int32_t)pool.size(); pool.insert(pool.end(), b.begin(), b.end());
       e[3] = nwv;
       vtab[d.H] = e;
     }
-    f.hc_off = htab[hk][0]; f.hw0_off = htab[hk][1];
+    f.hc_off = htab[hk][0]; f.hw0_off = htab[hk][1]; f.hperm_off = htab[hk][2];
     f.vc_off = vtab[d.H][0]; f.vg_off = vtab[d.H][1]; f.vb_off = vtab[d.H][2];
     auto& wl = fp->work[g.nw_class];
     for (int y0 = 0; y0 < p.out_h; y0 += d.band_rows) { wl.push_back(i); wl.push_back(y0); }
