@@ -293,3 +293,37 @@ def test_full_size_properties_cfg5_mixed_resolution():
     finally:
         plan.close()
         cudashm.destroy_shared_memory_region(region)
+
+
+@pytest.mark.parametrize("chunks", [1, 3, 8])
+def test_host_batch_pipeline_matches_oracle(chunks):
+    """Pinned host batch -> chunked H2D | kernel | D2H on two streams: every image must come back
+    equal to the oracle, whatever the chunking (11 images do not divide evenly)."""
+    import torch
+
+    from triton_client_b200.image_client import HostBatchPipeline
+    from triton_client_b200.utils import cuda_shared_memory as cudashm
+
+    n, H, W = 11, 240, 320
+    rng = np.random.default_rng(77)
+    src = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    h_in = torch.from_numpy(src).pin_memory()
+    pipe = HostBatchPipeline(n, W, H, 3, 2, "FP32", 3, 56, 72, "INCEPTION", chunks=chunks)
+    nbytes = n * pipe.out_bytes_per_image
+    h_out = torch.zeros(nbytes, dtype=torch.uint8).pin_memory()
+    region = cudashm.create_shared_memory_region("pipe", nbytes, 0)
+    try:
+        for _ in range(2):  # a second run reuses plans, streams and events
+            h_out.zero_()
+            pipe.run(h_in.data_ptr(), region._base_addr, nbytes, h_out.data_ptr())
+            torch.cuda.synchronize()
+            got = h_out.numpy().view(np.float32).reshape(n, 3, 56, 72)
+            for i in range(n):
+                assert np.array_equal(got[i], oracle_preprocess(src[i], 3, 56, 72, 2, "FP32", "INCEPTION")), i
+        on_dev = cudashm.get_contents_as_numpy(region, np.float32, [n, 3, 56, 72])
+        assert np.array_equal(on_dev, got)
+        with pytest.raises(ValueError):
+            pipe.run(h_in.data_ptr(), region._base_addr, nbytes - 1, None)
+    finally:
+        pipe.close()
+        cudashm.destroy_shared_memory_region(region)

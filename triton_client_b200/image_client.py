@@ -149,6 +149,71 @@ def preprocess_batch(images, format, dtype, c, h, w, scaling, out=None, out_offs
     return out, plan
 
 
+class HostBatchPipeline:
+    """Pinned host images -> region (-> pinned host result), for batches of equally sized images.
+
+    The batch is cut into ``chunks`` pieces; the host-to-device copy of piece k+1 runs on its own
+    stream while piece k is resampled and its result is read back on a second stream, so the two
+    PCIe directions and the kernel overlap (the reference does a pageable copy per array and one
+    synchronisation at the end, cuda_shared_memory/__init__.py:212-231). ``run`` is asynchronous
+    with respect to torch's current stream: work is ordered after it and it waits for the end."""
+
+    def __init__(self, n, width, height, src_channels, format, dtype, c, h, w, scaling, device=None, chunks=8):
+        import torch
+
+        self.device = current_device() if device is None else int(device)
+        self.n = int(n)
+        chunks = max(1, min(int(chunks), self.n))
+        self.bounds = [self.n * k // chunks for k in range(chunks + 1)]
+        self.img_bytes = int(width) * int(height) * int(src_channels)
+        dev = "cuda:%d" % self.device
+        self.stage = torch.empty(self.n * self.img_bytes, dtype=torch.uint8, device=dev)
+        self.plans = []
+        for k in range(chunks):
+            m = self.bounds[k + 1] - self.bounds[k]
+            self.plans.append(PreprocessPlan([(int(width), int(height), int(src_channels))] * m, format, dtype,
+                                             c, h, w, scaling, device=self.device))
+        self.out_bytes_per_image = self.plans[0].out_bytes_per_image
+        self.s_in = torch.cuda.Stream(device=self.device)
+        self.s_out = torch.cuda.Stream(device=self.device)
+        self.events = [torch.cuda.Event() for _ in range(chunks)]
+
+    def run(self, host_ptr, dst_ptr, dst_capacity, host_out_ptr=None):
+        """host_ptr: pinned host address of the n images back to back; dst_ptr: device address
+        (normally a region base) that receives n * out_bytes_per_image bytes; host_out_ptr: pinned
+        host address that receives a copy of the result (None: leave it on the device)."""
+        import torch
+
+        if dst_capacity < self.n * self.out_bytes_per_image:
+            raise ValueError("destination holds %d bytes, the batch needs %d"
+                             % (dst_capacity, self.n * self.out_bytes_per_image))
+        cur = torch.cuda.current_stream(self.device)
+        self.s_in.wait_stream(cur)
+        self.s_out.wait_stream(cur)
+        base = self.stage.data_ptr()
+        for k, plan in enumerate(self.plans):
+            i0, i1 = self.bounds[k], self.bounds[k + 1]
+            nb = (i1 - i0) * self.img_bytes
+            _lib.check(_lib.lib.TcbMemcpy(self.device, base + i0 * self.img_bytes, int(host_ptr) + i0 * self.img_bytes,
+                                          nb, self.s_in.cuda_stream, 0))
+            self.events[k].record(self.s_in)
+            self.s_out.wait_event(self.events[k])
+            ob = (i1 - i0) * self.out_bytes_per_image
+            plan.run([base + i * self.img_bytes for i in range(i0, i1)], int(dst_ptr) + i0 * self.out_bytes_per_image,
+                     ob, stream=self.s_out.cuda_stream)
+            if host_out_ptr is not None:
+                _lib.check(_lib.lib.TcbMemcpy(self.device, int(host_out_ptr) + i0 * self.out_bytes_per_image,
+                                              int(dst_ptr) + i0 * self.out_bytes_per_image, ob,
+                                              self.s_out.cuda_stream, 0))
+        cur.wait_stream(self.s_in)
+        cur.wait_stream(self.s_out)
+
+    def close(self):
+        for p in self.plans:
+            p.close()
+        self.plans = []
+
+
 def _pil_to_array(img, c):
     """uint8 array [H, W, Cin] of the PIL image. L / RGB / RGBA pixels are handed to the GPU as
     they are (the kernels implement Pillow's conversions between them); any other mode (palette,
