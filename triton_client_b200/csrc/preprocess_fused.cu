@@ -23,6 +23,7 @@
 #include <array>
 #include <cstdlib>
 #include <map>
+#include <type_traits>
 
 #include "preprocess.cuh"
 
@@ -105,7 +106,7 @@ struct FusedDesc {
   int32_t wq;        // words per planar row incl. padding
   int32_t stage_bytes;
   int32_t nst;       // TMA stages
-  int32_t aligned4;  // rows start 4-byte aligned: PRMT de-interleave applies
+  int32_t aligned4;  // rows start 4-byte aligned: the de-interleave reads them without funnel shifts
 };
 
 __device__ __forceinline__ uint32_t fetch_conv(const uint8_t* row, int cin, int C, int x, int ch) {
@@ -193,13 +194,9 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   const int tmp_idx0 = nchw ? xx : xx * C;      // + ch * (nchw ? out_w : 1)
   const int tmp_chs = nchw ? out_w : 1;
   const int nwords = (d.W + 3) >> 2;
-  const bool fast3 = d.aligned4 && d.cin == 3 && C == 3;
-  const bool fast1 = d.aligned4 && d.cin == 1 && C == 1;
-  // de-interleave work split (fast3 path): idle-in-H threads take dshare words each = dfirst words
-  const int n_idle = nthreads - min(out_w, nthreads);
-  const int dshare = 0;  // (experiment: give idle-in-H threads more de-interleave work) measured slower
-  (void)n_idle;
-  const int dfirst = min(nwords, n_idle * dshare);
+  const bool fast3 = d.cin == 3 && C == 3;  // word-wise de-interleave (rows of any alignment)
+  const bool fast1 = d.cin == 1 && C == 1;
+  const bool rows_al4 = d.aligned4 != 0;
   // vertical pass: units of 4 consecutive output elements; unit -> (line, x4) fixed per thread
   const bool vec4 = dst_aligned16 && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));
   const int upl = nchw ? out_w / 4 : L / 4;  // units per line (vec4 only)
@@ -219,42 +216,55 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
     uint4* Pb = P4;
     const uint8_t* r0 = stage + lead;
     if (fast3) {
-      // threads beyond out_w have no horizontal-pass work: they take `dshare` words each first,
-      // the rest is spread over everybody
-      for (int it = 0;; it++) {
-        int w;
-        if (it < dshare) {
-          if (tid < out_w) continue;
-          w = (tid - out_w) * dshare + it;
-          if (w >= dfirst) continue;
-        } else {
-          w = dfirst + (it - dshare) * nthreads + tid;
-          if (dfirst + (it - dshare) * nthreads >= nwords) break;
-          if (w >= nwords) continue;
-        }
-        uint32_t R[4], G[4], B[4];
+      // AL: rows start on 4-byte boundaries (compile-time, so the aligned loop carries no trace of
+      // the other one); otherwise (odd pitch: width not a multiple of 4) aligned words are read
+      // and funnel-shifted into place.
+      auto loop3 = [&](auto AL) {
+        for (int w = tid; w < nwords; w += nthreads) {
+          uint32_t R[4], G[4], B[4];
 #pragma unroll
-        for (int r = 0; r < 4; r++) {
-          uint32_t x0 = 0, x1 = 0, x2 = 0;
-          if (r < nrows) {
-            const uint32_t* rp = reinterpret_cast<const uint32_t*>(r0 + r * d.pitch) + 3 * w;
-            x0 = rp[0]; x1 = rp[1]; x2 = rp[2];  // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+          for (int r = 0; r < 4; r++) {
+            uint32_t x0 = 0, x1 = 0, x2 = 0;
+            if (r < nrows) {
+              const uint8_t* bp = r0 + r * d.pitch + 12 * w;
+              if (decltype(AL)::value) {
+                const uint32_t* rp = reinterpret_cast<const uint32_t*>(bp);
+                x0 = rp[0]; x1 = rp[1]; x2 = rp[2];  // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+              } else {
+                const uint32_t sh = (smem_u32(bp) & 3u) * 8u;
+                const uint32_t* rp = reinterpret_cast<const uint32_t*>(bp - (sh >> 3));
+                const uint32_t y0 = rp[0], y1 = rp[1], y2 = rp[2], y3 = rp[3];
+                x0 = __funnelshift_r(y0, y1, sh); x1 = __funnelshift_r(y1, y2, sh); x2 = __funnelshift_r(y2, y3, sh);
+              }
+            }
+            R[r] = __byte_perm(__byte_perm(x0, x1, 0x0630), x2, 0x5210);
+            G[r] = __byte_perm(__byte_perm(x0, x1, 0x0741), x2, 0x6210);
+            B[r] = __byte_perm(__byte_perm(x0, x1, 0x0052), x2, 0x7410);
           }
-          R[r] = __byte_perm(__byte_perm(x0, x1, 0x0630), x2, 0x5210);
-          G[r] = __byte_perm(__byte_perm(x0, x1, 0x0741), x2, 0x6210);
-          B[r] = __byte_perm(__byte_perm(x0, x1, 0x0052), x2, 0x7410);
+          const int pw = p4_phys(w);
+          Pb[pw] = make_uint4(R[0], R[1], R[2], R[3]);
+          Pb[(C > 1 ? 1 : 0) * wqp + pw] = make_uint4(G[0], G[1], G[2], G[3]);
+          Pb[(C > 2 ? 2 : 0) * wqp + pw] = make_uint4(B[0], B[1], B[2], B[3]);
         }
-        const int pw = p4_phys(w);
-        Pb[pw] = make_uint4(R[0], R[1], R[2], R[3]);
-        Pb[(C > 1 ? 1 : 0) * wqp + pw] = make_uint4(G[0], G[1], G[2], G[3]);
-        Pb[(C > 2 ? 2 : 0) * wqp + pw] = make_uint4(B[0], B[1], B[2], B[3]);
-      }
+      };
+      if (rows_al4) loop3(std::true_type{}); else loop3(std::false_type{});
     } else if (fast1) {
       for (int w = tid; w < nwords; w += nthreads) {
         uint32_t v[4];
 #pragma unroll
-        for (int r = 0; r < 4; r++)
-          v[r] = r < nrows ? reinterpret_cast<const uint32_t*>(r0 + r * d.pitch)[w] : 0u;
+        for (int r = 0; r < 4; r++) {
+          v[r] = 0u;
+          if (r < nrows) {
+            const uint8_t* bp = r0 + r * d.pitch + 4 * w;
+            if (rows_al4) {
+              v[r] = *reinterpret_cast<const uint32_t*>(bp);
+            } else {
+              const uint32_t sh = (smem_u32(bp) & 3u) * 8u;
+              const uint32_t* rp = reinterpret_cast<const uint32_t*>(bp - (sh >> 3));
+              v[r] = __funnelshift_r(rp[0], rp[1], sh);
+            }
+          }
+        }
         Pb[p4_phys(w)] = make_uint4(v[0], v[1], v[2], v[3]);
       }
     } else {  // any channel conversion / rows not 4-byte aligned: byte-wise
