@@ -103,6 +103,7 @@ __device__ __forceinline__ int find_image(const int32_t* __restrict__ blk, int n
 }
 
 constexpr int kTwoPassThreads = 256;
+constexpr int kPass2Px = 8;  // output pixels per thread of pass 2 (amortises the image lookup and descriptor load)
 
 // Pass 1: first separable pass into the uint8 intermediate tmp[p1_h][p1_w][C].
 template <int C>
@@ -160,15 +161,10 @@ k_resample_pass2(const ImgDesc* __restrict__ descs, const int32_t* __restrict__ 
                  const int32_t* __restrict__ pool, const uint8_t* __restrict__ scratch,
                  const uint8_t* __restrict__ lut, uint8_t* __restrict__ dst, int out_h, int out_w,
                  int layout) {
-  __shared__ __align__(16) uint8_t s_lut[C * 256 * ELEM];
-  for (int i = threadIdx.x; i < C * 256 * ELEM / 4; i += kTwoPassThreads)
-    reinterpret_cast<uint32_t*>(s_lut)[i] = reinterpret_cast<const uint32_t*>(lut)[i];
-  __syncthreads();
+  // the value table (C x 256 entries) is read straight from global memory: it stays in L1, and
+  // copying it to shared memory cost every 256-pixel block three times its own payload
   const int img = find_image(blk, n, blockIdx.x);
   const ImgDesc d = descs[img];
-  const int local = (blockIdx.x - blk[img]) * kTwoPassThreads + threadIdx.x;
-  if (local >= out_h * out_w) return;
-  const int y = local / out_w, x = local - y * out_w;
   // input of this pass: the intermediate of pass 1, or the (converted) source image
   const uint8_t* in;
   int in_pitch, in_cin;
@@ -177,6 +173,12 @@ k_resample_pass2(const ImgDesc* __restrict__ descs, const int32_t* __restrict__ 
   } else {
     in = d.src; in_pitch = d.pitch; in_cin = d.cin;
   }
+  uint8_t* o = dst + (size_t)img * C * out_h * out_w * ELEM;
+  const int local0 = (blockIdx.x - blk[img]) * (kTwoPassThreads * kPass2Px) + threadIdx.x;
+  for (int px = 0; px < kPass2Px; px++) {  // consecutive threads take consecutive pixels in every round
+  const int local = local0 + px * kTwoPassThreads;
+  if (local >= out_h * out_w) return;
+  const int y = local / out_w, x = local - y * out_w;
   int u[C];
   int v[C];
   if (d.p2_axis == AXIS_NONE) {
@@ -208,12 +210,12 @@ k_resample_pass2(const ImgDesc* __restrict__ descs, const int32_t* __restrict__ 
 #pragma unroll
     for (int ch = 0; ch < C; ch++) u[ch] = clip8(acc[ch]);
   }
-  uint8_t* o = dst + (size_t)img * C * out_h * out_w * ELEM;
 #pragma unroll
   for (int ch = 0; ch < C; ch++) {
     const size_t idx = layout == TCB_LAYOUT_NCHW ? ((size_t)ch * out_h + y) * out_w + x
                                                  : ((size_t)y * out_w + x) * C + ch;
-    store_elem<ELEM>(o, idx, s_lut + ((size_t)ch * 256 + u[ch]) * ELEM);
+    store_elem<ELEM>(o, idx, lut + ((size_t)ch * 256 + u[ch]) * ELEM);
+  }
   }
 }
 
@@ -377,7 +379,7 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
     } else {
       blk1[i + 1] = blk1[i];
     }
-    blk2[i + 1] = blk2[i] + (out_h * out_w + kTwoPassThreads - 1) / kTwoPassThreads;
+    blk2[i + 1] = blk2[i] + (out_h * out_w + kTwoPassThreads * kPass2Px - 1) / (kTwoPassThreads * kPass2Px);
   }
   p->blocks1 = blk1[n_images]; p->blocks2 = blk2[n_images];
   p->scratch_bytes = scratch; p->pool_words = pool.size();
