@@ -55,27 +55,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// Wait with a time bound: a protocol bug becomes a trapped kernel (an error code on the host)
-// instead of a hung GPU.
-__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
-  uint32_t done = 0;
-  const long long t0 = clock64();
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    if (done) return;
-    __nanosleep(40);  // waiting warps must not eat the issue slots of working warps
-    if (clock64() - t0 > 8000000000ll) __trap();
-  }
-}
 // 1-D TMA: global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -105,7 +84,6 @@ struct FusedDesc {
   int32_t band_rows;
   int32_t wq;        // words per planar row incl. padding
   int32_t stage_bytes;
-  int32_t nst;       // TMA stages
   int32_t aligned4;  // rows start 4-byte aligned: the de-interleave reads them without funnel shifts
 };
 
@@ -567,7 +545,7 @@ static int nw_class(int nw) {
 }
 
 struct FusedGeom {
-  int nw_class, nwv, wq, stage_bytes, nst, threads;
+  int nw_class, nwv, wq, stage_bytes, threads;
   size_t smem;
 };
 
@@ -592,7 +570,6 @@ static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc&
   g->wq = p4_phys(((d.W + 3) >> 2) + cls + 1) + 1;  // physical granules per plane
   g->stage_bytes = (int)round_up((uint64_t)4 * d.pitch + 48, 128);
   g->threads = out_w > 256 ? 512 : 256;
-  g->nst = 2;
   g->smem = 64 + (size_t)g->stage_bytes + (size_t)c * g->wq * 16 + (size_t)(nwv + 1) * out_w * c * 4 + 64;
   return g->smem <= kFusedMaxSmem;
 }
@@ -670,7 +647,7 @@ int fused_prepare(Plan& p) {
     FusedDesc& f = fp->desc[i];
     f.src = d.src; f.W = d.W; f.H = d.H; f.pitch = d.pitch; f.cin = d.cin;
     f.nw = g.nw_class; f.nwv = g.nwv; f.band_rows = d.band_rows; f.wq = g.wq;
-    f.stage_bytes = g.stage_bytes; f.nst = g.nst;
+    f.stage_bytes = g.stage_bytes;
     f.aligned4 = (reinterpret_cast<uintptr_t>(d.src) % 4 == 0) && (d.pitch % 4 == 0);
     auto hk = std::make_pair(d.W, g.nw_class);
     if (!htab.count(hk)) {
