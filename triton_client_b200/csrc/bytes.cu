@@ -780,11 +780,31 @@ __global__ void __launch_bounds__(kDesThreads)
 k_des_speculate(const uint8_t* __restrict__ stream4, unsigned int bias, unsigned long long S,
                 unsigned long long K, DesArrays A) {
   __shared__ unsigned int s_votes[kDesWarps][kDesWindow];
+  __shared__ unsigned int s_win[kDesWarps][kDesWindow / 4 + 4];  // look-behind window (+ 16 bytes) of one chunk
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned long long kbase = ((unsigned long long)blockIdx.x * kDesWarps + warp) * 32;
   if (kbase >= K) return;
   unsigned int* votes = s_votes[warp];
+  unsigned int* win = s_win[warp];
   auto load_len = [&](unsigned long long pos) { return ldg_u32_unaligned(stream4, pos + bias); };
+  const unsigned long long S4 = (S + bias + 3) >> 2;  // words of stream4 that hold stream bytes
+  constexpr int kWinWords = kDesWindow / 4 + 4;
+  constexpr int kWinPerLane = (kWinWords + 31) / 32;
+  // The window of a chunk is fetched with ONE coalesced round trip (and the next chunk's window
+  // while this one is voted on): read word by word from global memory, every 32-byte step of the
+  // candidate loop was a fresh DRAM sector and the vote cost two thirds of the kernel.
+  auto fetch_window = [&](unsigned long long k, unsigned int (&w)[kWinPerLane]) {
+    const unsigned long long w0 = (k * kDesChunk - kDesWindow) >> 2;  // first word (stream4 is 4-byte aligned)
+#pragma unroll
+    for (int i = 0; i < kWinPerLane; i++) {
+      const unsigned long long wi = w0 + (unsigned long long)i * 32 + lane;
+      w[i] = (i * 32 + lane < kWinWords && wi < S4) ? __ldg(reinterpret_cast<const uint32_t*>(stream4) + wi) : 0u;
+    }
+  };
+  unsigned int wnext[kWinPerLane];
+#pragma unroll
+  for (int i = 0; i < kWinPerLane; i++) wnext[i] = 0;
+  if (kbase + (kbase == 0 ? 1 : 0) < K) fetch_window(kbase + (kbase == 0 ? 1 : 0), wnext);
 
   unsigned long long my_g = kNoGuess;
   for (int j = 0; j < 32; j++) {
@@ -795,14 +815,27 @@ k_des_speculate(const uint8_t* __restrict__ stream4, unsigned int bias, unsigned
       continue;
     }
     const unsigned long long c0 = k * kDesChunk;
+    // publish this chunk's window, start the next one's loads
+#pragma unroll
+    for (int i = 0; i < kWinPerLane; i++)
+      if (i * 32 + lane < kWinWords) win[i * 32 + lane] = wnext[i];
     for (int i = lane; i < kDesWindow; i += 32) votes[i] = 0;
+    if (j + 1 < 32 && k + 1 < K) fetch_window(k + 1, wnext);
     __syncwarp();
+    // window byte b (0 = stream position c0 - kDesWindow) sits at byte b + bias of win[]
+    auto win_len = [&](unsigned int b) {
+      const unsigned int q = b + bias;
+      const unsigned int lo = win[q >> 2];
+      const unsigned int sh = (q & 3) * 8;
+      return sh ? __funnelshift_r(lo, win[(q >> 2) + 1], sh) : lo;
+    };
+    const unsigned long long wbase = c0 - kDesWindow;
     for (int it = 0; it < kDesWindow / 32; it++) {
-      unsigned long long pos = c0 - kDesWindow + it * 32 + lane;
+      unsigned long long pos = wbase + it * 32 + lane;
       bool ok = true;
       while (pos < c0) {
         if (pos + 4 > S) { ok = false; break; }
-        const unsigned long long nx = pos + 4 + load_len(pos);
+        const unsigned long long nx = pos + 4 + win_len((unsigned int)(pos - wbase));
         if (nx > S) { ok = false; break; }
         pos = nx;
       }
