@@ -157,17 +157,17 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   const bool nchw = layout == TCB_LAYOUT_NCHW;
   const int xx = pool[d.hperm_off + tid];  // output column of this thread (>= out_w: none), see lane_columns()
   uint32_t kc[NW][3];
-  int poff[NW];  // physical granule offsets of this column's NW source words
+  int pw0 = 0;  // first P4 granule of this column (p4_phys is the identity: the NW granules are consecutive)
 #pragma unroll
-  for (int j = 0; j < NW; j++) { kc[j][0] = 0; kc[j][1] = 0; kc[j][2] = 0; poff[j] = 0; }
+  for (int j = 0; j < NW; j++) { kc[j][0] = 0; kc[j][1] = 0; kc[j][2] = 0; }
   if (xx < out_w) {
     const int w0 = pool[d.hw0_off + xx];
     const int32_t* hc = pool + d.hc_off + (size_t)xx * NW * 3;
 #pragma unroll
     for (int j = 0; j < NW; j++) {
       kc[j][0] = hc[j * 3 + 0]; kc[j][1] = hc[j * 3 + 1]; kc[j][2] = hc[j * 3 + 2];
-      poff[j] = p4_phys(w0 + j);
     }
+    pw0 = w0;
   }
   const int tmp_idx0 = nchw ? xx : xx * C;      // + ch * (nchw ? out_w : 1)
   const int tmp_chs = nchw ? out_w : 1;
@@ -182,6 +182,9 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   const int32_t* vg = pool + d.vg_off;
   uint8_t* dimg = dst + (size_t)img * C * out_h * out_w * elem;
   int yy_next = yy0;
+  // (first group, last group) of the next output row to finish, kept in registers so that the
+  // per-phase test does not wait for a global load
+  int vg_first = vg[2 * yy0], vg_last = vg[2 * yy0 + 1];
   const int my_ln = (nchw && upl > 0) ? tid / upl : 0;  // this thread's first unit, hoisted out of the row loop
   const int my_x4 = (nchw && upl > 0) ? tid - my_ln * upl : tid;
 
@@ -290,7 +293,7 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
     }
   }
   auto vertical = [&](int yy, int g_now, int slot_now) {
-    const int gv0 = vg[2 * yy];
+    const int gv0 = vg_first;
     const uint4* vc = reinterpret_cast<const uint4*>(pool + d.vc_off) + (size_t)yy * d.nwv;  // [nwv] x (k0, k1, k2, -)
     // ring slot of the row's first group: the group being written now sits in slot_now and the row
     // reaches back at most nwv = ng - 1 groups
@@ -406,7 +409,7 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
           const uint4* p = Pb + ch * wqp;
 #pragma unroll
           for (int j = 0; j < NW; j++) {
-            const uint4 v = p[poff[j]];
+            const uint4 v = p[pw0 + j];
             a[0][0] = __dp4a(v.x, kc[j][0], a[0][0]); a[0][1] = __dp4a(v.x, kc[j][1], a[0][1]); a[0][2] = __dp4a(v.x, kc[j][2], a[0][2]);
             a[1][0] = __dp4a(v.y, kc[j][0], a[1][0]); a[1][1] = __dp4a(v.y, kc[j][1], a[1][1]); a[1][2] = __dp4a(v.y, kc[j][2], a[1][2]);
             a[2][0] = __dp4a(v.z, kc[j][0], a[2][0]); a[2][1] = __dp4a(v.z, kc[j][1], a[2][1]); a[2][2] = __dp4a(v.z, kc[j][2], a[2][2]);
@@ -420,7 +423,11 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
       }
     }
     // vertical pass of the rows whose last group was written in an earlier phase
-    while (yy_next < yy1 && vg[2 * yy_next + 1] < g) vertical(yy_next++, g, slot);
+    while (yy_next < yy1 && vg_last < g) {
+      vertical(yy_next, g, slot);
+      yy_next++;
+      if (yy_next < yy1) { vg_first = vg[2 * yy_next]; vg_last = vg[2 * yy_next + 1]; }
+    }
     if (i < n_groups) {
       __syncthreads();  // P4 free again, tmp4 slot visible
       if (++slot == ng) slot = 0;
