@@ -241,6 +241,31 @@ def test_unaligned_and_pitched_sources():
     plan.close()
 
 
+def test_plan_reused_with_differently_aligned_sources():
+    """A plan created with 4-byte aligned sources must stay correct when a later run hands it
+    sources that start 1, 2 or 3 bytes off (and back): the row-alignment flag the fused kernel
+    reads is refreshed with the pointers."""
+    import torch
+
+    from triton_client_b200.image_client import PreprocessPlan
+
+    rng = np.random.default_rng(9)
+    W, H = 640, 360
+    img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    ref = oracle_preprocess(img, 3, 224, 224, 2, "FP32", "VGG")
+    buf = torch.zeros(H * W * 3 + 64, dtype=torch.uint8, device="cuda")
+    plan = PreprocessPlan([(W, H, 3)], 2, "FP32", 3, 224, 224, "VGG", device=0)
+    out = torch.zeros(plan.out_bytes_per_image, dtype=torch.uint8, device="cuda")
+    for off in (0, 1, 16, 3, 2, 0):
+        buf[off: off + H * W * 3].copy_(torch.from_numpy(img).reshape(-1))
+        out.zero_()
+        plan.run([buf.data_ptr() + off], out.data_ptr(), out.numel())
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy().view(np.float32).reshape(3, 224, 224), ref), off
+    assert plan.info()["fused_images"] == 1
+    plan.close()
+
+
 def test_full_size_properties_cfg5_mixed_resolution():
     """cfg5 at full size: 8192 mixed-resolution images (SURVEY.md 8d size menu, drawn with
     default_rng(1234).choice) -> 224x224 fp16 NHWC INCEPTION in one region. Checked through

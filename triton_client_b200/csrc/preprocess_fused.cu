@@ -724,7 +724,12 @@ int fused_update_sources(const Plan& p, cudaStream_t s) {
   if (it == registry().end()) return TCB_OK;
   FusedPlan* fp = it->second;
   for (int i = 0; i < p.n; i++)
-    if (p.h_desc[i].fused) { fp->desc[i].src = p.h_desc[i].src; fp->desc[i].pitch = p.h_desc[i].pitch; }
+    if (p.h_desc[i].fused) {
+      FusedDesc& f = fp->desc[i];
+      f.src = p.h_desc[i].src;
+      f.pitch = p.h_desc[i].pitch;
+      f.aligned4 = (reinterpret_cast<uintptr_t>(f.src) % 4 == 0) && (f.pitch % 4 == 0);  // may change from run to run
+    }
   TCB_CUDA(cudaMemcpyAsync(fp->d_desc, fp->desc.data(), sizeof(FusedDesc) * p.n, cudaMemcpyHostToDevice, s));
   return TCB_OK;
 }
