@@ -169,7 +169,9 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
     }
     pw0 = w0;
   }
-  const int tmp_idx0 = nchw ? xx : xx * C;      // + ch * (nchw ? out_w : 1)
+  // first tmp4 word of this thread's column (+ ch * tmp_chs), or -1: no column. The test in the main
+  // loop reads this register, which the horizontal pass needs anyway, instead of keeping xx alive.
+  const int tmp_idx0 = xx < out_w ? (nchw ? xx : xx * C) : -1;
   const int tmp_chs = nchw ? out_w : 1;
   const int nwords = (d.W + 3) >> 2;
   const bool fast3 = d.cin == 3 && C == 3;  // word-wise de-interleave (rows of any alignment)
@@ -398,7 +400,7 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
       deinterleave(i);
       __syncthreads();  // raw stage drained, P4 complete
       if (tid == 0 && i + 1 < n_groups) issue(i + 1);
-      if (xx < out_w) {
+      if (tmp_idx0 >= 0) {
         const uint4* Pb = P4;
         uint32_t* out = tmp4 + (size_t)slot * L + tmp_idx0;
 #pragma unroll
@@ -424,9 +426,12 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
     }
     // vertical pass of the rows whose last group was written in an earlier phase
     while (yy_next < yy1 && vg_last < g) {
+      // the next row's bookkeeping is requested before this row's work and consumed after it
+      const int nxt = min(yy_next + 1, yy1 - 1);
+      const int nf = vg[2 * nxt], nl = vg[2 * nxt + 1];
       vertical(yy_next, g, slot);
       yy_next++;
-      if (yy_next < yy1) { vg_first = vg[2 * yy_next]; vg_last = vg[2 * yy_next + 1]; }
+      vg_first = nf; vg_last = nl;
     }
     if (i < n_groups) {
       __syncthreads();  // P4 free again, tmp4 slot visible
