@@ -213,6 +213,26 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
                         uint64_t workspace_bytes, uint64_t* n_elements_host,
                         uint64_t* payload_bytes_host, void* stream);
 
+/* =============================================================================================
+ * BF16 tensors.
+ * Replaces tritonclient/utils/__init__.py:279-323 serialize_bf16_tensor (np.nditer +
+ * struct.pack("<f", x)[2:4] per element + b"".join) and :326-348 deserialize_bf16_tensor
+ * (unpack_from("<2s") + struct.unpack("<f", b"\x00\x00" + sb) per element).
+ * Wire format: per element, in C order, the upper 16 bits of the float32 bit pattern, little
+ * endian - plain truncation, no rounding. One quirk is kept: the reference goes through Python
+ * floats, which turns a signalling NaN into a quiet one (mantissa bit 22 set) in both directions.
+ * ============================================================================================= */
+
+/* src_f32_dev: n_elements float32 (4-byte aligned); dst_dev receives 2 * n_elements bytes
+ * (2-byte aligned; 128-bit stores are used when source and destination alignments agree). */
+int TcbBf16Serialize(int device_id, const void* src_f32_dev, uint64_t n_elements, void* dst_dev,
+                     uint64_t dst_capacity, void* stream);
+/* src_dev: src_bytes of bfloat16 wire data; dst_f32_dev receives src_bytes / 2 float32 values
+ * (low 16 bits zero). An odd src_bytes returns TCB_ERR_TRUNCATED where the reference's
+ * unpack_from raises struct.error. */
+int TcbBf16Deserialize(int device_id, const void* src_dev, uint64_t src_bytes, void* dst_f32_dev,
+                       uint64_t dst_capacity, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -168,3 +168,47 @@ def to_object_array(blob, lens):
     for i in range(len(lens)):
         arr[i] = b[off[i]:off[i + 1]]
     return arr
+
+
+# ---- BF16 wire codec (utils/__init__.py:279-348) ---------------------------------------------
+
+
+def bf16_serialize_elements(input_tensor):
+    """utils/__init__.py:279-323, per element: ``struct.pack("<f", x)[2:4]`` in logical C order.
+    Returns the wire ``bytes`` (the reference wraps them in a 0-d object array)."""
+    if input_tensor.size == 0:
+        return b""
+    if input_tensor.dtype != np.float32:
+        raise OracleError("cannot serialize bf16 tensor: invalid datatype")
+    parts = []
+    for obj in np.nditer(input_tensor, flags=["refs_ok"], order="C"):
+        parts.append(struct.pack("<f", obj)[2:4])
+    return b"".join(parts)
+
+
+def bf16_serialize(input_tensor):
+    """Vectorised statement of the same thing: the upper 16 bits of every float32 pattern,
+    little endian (truncation, no rounding). One subtlety, found by comparing with the reference on
+    raw bit patterns: ``struct.pack("<f", obj)`` goes through a Python float (a double), and that
+    round trip turns a signalling NaN into a quiet one - mantissa bit 22 is set before the cut, so
+    0x7F800001 becomes 0x7FC0 and not the infinity 0x7F80."""
+    bits = np.ascontiguousarray(input_tensor, dtype=np.float32).reshape(-1).view(np.uint32)
+    nan = (bits & np.uint32(0x7FFFFFFF)) > np.uint32(0x7F800000)
+    bits = np.where(nan, bits | np.uint32(0x00400000), bits)
+    return (bits >> 16).astype("<u2").tobytes()
+
+
+def bf16_deserialize(buf):
+    """utils/__init__.py:326-348: ``b"\\x00\\x00" + two bytes`` -> float32. The reference appends
+    the 1-tuples ``struct.unpack`` returns, hence the (n, 1) result shape (``(0,)`` when empty); an
+    odd trailing byte raises ``struct.error``."""
+    buf = bytes(buf)
+    if len(buf) == 0:
+        return np.array([], dtype=np.float32)
+    if len(buf) & 1:
+        raise struct.error("unpack_from requires a buffer of at least %d bytes for unpacking 2 bytes at offset %d "
+                           "(actual buffer size is %d)" % (len(buf) + 1, len(buf) - 1, len(buf)))
+    bits = np.frombuffer(buf, dtype="<u2").astype(np.uint32) << 16
+    nan = (bits & np.uint32(0x7FFFFFFF)) > np.uint32(0x7F800000)
+    bits = np.where(nan, bits | np.uint32(0x00400000), bits)  # unpack -> Python float -> float32 quiets NaNs
+    return bits.view(np.float32).reshape(-1, 1)

@@ -140,3 +140,29 @@ def object_cases():
     c["ref_string_infer_bytes_"] = np.array([[b"\x00\x01\x02\x03"] * 16], dtype=np.bytes_)
     c["ref_cc_client_test"] = np.array([b"\x01\x7f", b"\x02\x7f"], dtype=np.object_)
     return c
+
+
+# ---- BF16 codec cases ----------------------------------------------------------------------------
+BF16_SEED = 77
+
+
+def bf16_cases():
+    """name -> float32 ndarray. Specials (NaN with payload, +-Inf, denormals, -0, max), a
+    non-contiguous view, a Fortran-ordered array and a seeded random block of raw bit patterns."""
+    rng = np.random.default_rng(BF16_SEED)
+    specials = np.array([0x00000000, 0x80000000, 0x7F800000, 0xFF800000, 0x7FC00000, 0x7FC12345, 0xFFFFFFFF,
+                         0x00000001, 0x00007FFF, 0x00008000, 0x0000FFFF, 0x00010000, 0x007FFFFF, 0x7F7FFFFF,
+                         0x3F800000, 0x3F80FFFF, 0x3F808000, 0x3F807FFF, 0xC0490FDB,
+                         0x7F800001, 0xFF800001, 0x7FA00000, 0x7FBFFFFF, 0xFF80FFFF], dtype=np.uint32).view(np.float32)
+    raw = rng.integers(0, 1 << 32, 4099, dtype=np.uint64).astype(np.uint32).view(np.float32)
+    mat = rng.standard_normal((37, 53)).astype(np.float32)
+    return {
+        "specials": specials,
+        "raw_bits_4099": raw,
+        "scalar_0d": np.float32(3.14159).reshape(()),
+        "matrix": mat,
+        "transposed_view": mat.T,
+        "strided_view": mat[::3, 1::2],
+        "fortran": np.asfortranarray(mat),
+        "single": np.array([1.5], dtype=np.float32),
+    }

@@ -79,6 +79,19 @@ def main():
                               "result_shape": list(r.shape), "result_dtype": str(r.dtype)})
     with open(os.path.join(HERE, "bytes_golden.json"), "w") as f:
         json.dump(bg, f, indent=1)
+    # ---- BF16 -------------------------------------------------------------------------------
+    bf = {"env": env, "cases": []}
+    for name, arr in cases.bf16_cases().items():
+        r = utils.serialize_bf16_tensor(arr)
+        ser = r.item()
+        back = utils.deserialize_bf16_tensor(ser)
+        bf["cases"].append({"name": name, "n": int(arr.size), "serialized_sha256": sha(ser),
+                            "serialized_hex": ser.hex() if len(ser) <= 64 else None,
+                            "result_shape": list(r.shape), "result_dtype": str(r.dtype),
+                            "back_shape": list(back.shape), "back_dtype": str(back.dtype),
+                            "back_sha256": sha(np.ascontiguousarray(back).tobytes())})
+    with open(os.path.join(HERE, "bf16_golden.json"), "w") as f:
+        json.dump(bf, f, indent=1)
     print("wrote goldens:", len(gold["cases"]), "preprocess cases,", len(bg["gbytes"]), "gbytes,",
           len(bg["objects"]), "object cases")
 

@@ -197,3 +197,46 @@ def test_restatements_equal_reference_live():
         ser = r.item() if r.size else b""
         assert bc.serialize_elements(arr) == ser, name
         assert list(utils.deserialize_bytes_tensor(ser)) == bc.deserialize_stream(ser)
+
+
+# ---- BF16 codec: oracle restatements against goldens from the unmodified reference ----------------
+BF = json.load(open(os.path.join(GOLD, "bf16_golden.json")))
+
+
+@pytest.mark.parametrize("rec", BF["cases"], ids=[c["name"] for c in BF["cases"]])
+def test_bf16_oracle_matches_reference_golden(rec):
+    arr = cases.bf16_cases()[rec["name"]]
+    assert arr.size == rec["n"]
+    ser = bc.bf16_serialize(arr)
+    assert sha(ser) == rec["serialized_sha256"]
+    if arr.size <= 256:
+        assert bc.bf16_serialize_elements(arr) == ser
+    if rec["serialized_hex"] is not None:
+        assert ser.hex() == rec["serialized_hex"]
+    back = bc.bf16_deserialize(ser)
+    assert list(back.shape) == rec["back_shape"] and str(back.dtype) == rec["back_dtype"]
+    assert sha(np.ascontiguousarray(back).tobytes()) == rec["back_sha256"]
+
+
+def test_bf16_oracle_edges():
+    assert bc.bf16_deserialize(b"").shape == (0,)
+    with pytest.raises(struct.error):
+        bc.bf16_deserialize(b"abc")
+    with pytest.raises(bc.OracleError):
+        bc.bf16_serialize_elements(np.zeros(3, dtype=np.float64))
+
+
+@pytest.mark.skipif(not rl.available(), reason="/root/reference not mounted")
+def test_bf16_oracle_matches_reference_live():
+    u = rl.reference_utils()
+    for name, arr in cases.bf16_cases().items():
+        ser = u.serialize_bf16_tensor(arr).item()
+        assert bc.bf16_serialize(arr) == ser, name
+        ref_back = u.deserialize_bf16_tensor(ser)
+        got = bc.bf16_deserialize(ser)
+        assert got.shape == ref_back.shape and got.tobytes() == ref_back.tobytes(), name
+    with pytest.raises(struct.error) as e_ref:
+        u.deserialize_bf16_tensor(b"abcde")
+    with pytest.raises(struct.error) as e_or:
+        bc.bf16_deserialize(b"abcde")
+    assert str(e_ref.value) == str(e_or.value)

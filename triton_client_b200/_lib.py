@@ -35,6 +35,7 @@ EXPORTS = [
     "TcbPreprocessPlanDestroy", "TcbResampleCoeffs",
     "TcbBytesSerializeWorkspace", "TcbBytesDeserializeWorkspace", "TcbBytesSerialize",
     "TcbBytesSerializeFixedWidth", "TcbBytesDeserialize", "TcbBytesSerializeNoAlloc",
+    "TcbBf16Serialize", "TcbBf16Deserialize",
 ]
 
 
@@ -109,6 +110,8 @@ _sig("TcbBytesSerializeFixedWidth", c_int,
 _sig("TcbBytesDeserialize", c_int,
      [c_int, c_void_p, c_uint64, c_int64, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p,
       c_uint64, POINTER(c_uint64), POINTER(c_uint64), c_void_p])
+_sig("TcbBf16Serialize", c_int, [c_int, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p])
+_sig("TcbBf16Deserialize", c_int, [c_int, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p])
 
 
 def last_error():

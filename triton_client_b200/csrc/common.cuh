@@ -61,6 +61,13 @@ inline int sm_count(int device) {
   return n;
 }
 
+// pinned staging for large copies from/to pageable host memory (staging.cu)
+bool staging_applies(const void* host_ptr, uint64_t bytes);
+bool is_pageable_host(const void* p);
+bool is_device_ptr(const void* p);
+int staged_h2d(int device, void* dst_dev, const void* src_host, uint64_t bytes, cudaStream_t s);
+int staged_d2h(int device, void* dst_host, const void* src_dev, uint64_t bytes, cudaStream_t s);
+
 static inline uint64_t round_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }
 
 }  // namespace tcb

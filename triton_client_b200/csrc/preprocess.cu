@@ -427,35 +427,40 @@ int TcbPreprocessPlanRun(void* plan, const TcbImage* images_or_null, void* dst_d
   TCB_DEVICE_GUARD(p->device);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (images_or_null) {
+    // validate everything first, then commit: a failed run must leave the plan's host and device
+    // descriptors as they were
     bool changed = false;
     for (int i = 0; i < p->n; i++) {
       const TcbImage& im = images_or_null[i];
-      ImgDesc& d = p->h_desc[i];
+      const ImgDesc& d = p->h_desc[i];
       TCB_CHECK_ARG(im.width == d.W && im.height == d.H && im.src_channels == d.cin,
                     "TcbPreprocessPlanRun: image %d geometry differs from the plan", i);
       TCB_CHECK_ARG((int64_t)im.pitch >= (int64_t)im.width * im.src_channels,
                     "TcbPreprocessPlanRun: image %d pitch too small", i);
       const uint8_t* sp = reinterpret_cast<const uint8_t*>(im.src_dev);
       if (sp != d.src || im.pitch != d.pitch) {
-        if (d.fused) {
-          // the fused kernel's eligibility depends on pitch/alignment; re-check
-          ImgDesc t = d; t.src = sp; t.pitch = im.pitch;
-          int band; size_t smem;
-          if (!fused_supported(*p, t, &band, &smem) || band != d.band_rows || smem > p->fused_smem)
-            return set_error(TCB_ERR_UNSUPPORTED,
-                             "TcbPreprocessPlanRun: image %d pointer/pitch alignment differs from the "
-                             "plan's; create a new plan", i);
-        }
-        d.src = sp; d.pitch = im.pitch; changed = true;
+        // the fused kernel's eligibility depends on pitch/alignment; re-check
+        if (d.fused && !fused_accepts(*p, i, sp, im.pitch))
+          return set_error(TCB_ERR_UNSUPPORTED,
+                           "TcbPreprocessPlanRun: image %d pointer/pitch does not fit the plan's fused launch; "
+                           "create a new plan", i);
+        changed = true;
       }
     }
-    // pageable source: cudaMemcpyAsync returns once the host buffer has been staged
     if (changed) {
-      TCB_CUDA(cudaMemcpyAsync(p->d_desc, p->h_desc.data(), sizeof(ImgDesc) * p->n,
-                               cudaMemcpyHostToDevice, s));
-      int rc = fused_update_sources(*p, s);
-      if (rc) return rc;
+      for (int i = 0; i < p->n; i++) {
+        p->h_desc[i].src = reinterpret_cast<const uint8_t*>(images_or_null[i].src_dev);
+        p->h_desc[i].pitch = images_or_null[i].pitch;
+      }
+      p->desc_dirty = true;
     }
+  }
+  if (p->desc_dirty) {  // stays set until both uploads have been enqueued
+    // pageable source: cudaMemcpyAsync returns once the host buffer has been staged
+    TCB_CUDA(cudaMemcpyAsync(p->d_desc, p->h_desc.data(), sizeof(ImgDesc) * p->n, cudaMemcpyHostToDevice, s));
+    int rc = fused_update_sources(*p, s);
+    if (rc) return rc;
+    p->desc_dirty = false;
   }
   for (int i = 0; i < p->n; i++)
     TCB_CHECK_ARG(p->h_desc[i].src != nullptr, "TcbPreprocessPlanRun: image %d has no source pointer", i);

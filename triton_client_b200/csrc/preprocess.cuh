@@ -1,5 +1,7 @@
 // Shared declarations for the preprocess kernels (two-pass and fused).
 #pragma once
+#include <array>
+#include <map>
 #include <vector>
 
 #include "common.cuh"
@@ -30,6 +32,13 @@ struct ImgDesc {
   int32_t band_rows;           // fused kernel: output rows per CTA
 };
 
+// launch geometry of one image in the fused kernel (preprocess_fused.cu)
+struct FusedGeom {
+  int nw_class = 0, nwv = 0, wq = 0, stage_bytes = 0, threads = 0;
+  size_t smem = 0;
+  bool ok = false;
+};
+
 struct Plan {
   int device = 0;
   int n = 0, c = 0, out_h = 0, out_w = 0, layout = 0, elem = 0;
@@ -48,6 +57,11 @@ struct Plan {
   int32_t* d_fused_work = nullptr;  // pairs (image, first output row)
   int n_fused_ctas = 0, n_fused_images = 0;
   size_t fused_smem = 0;
+  bool desc_dirty = false;  // host descriptors changed, device copies not yet re-uploaded
+  // fused-kernel geometry per distinct (W, H, channels, pitch): a batch of thousands of images has a
+  // handful of distinct sizes, and the coefficient set-up behind the answer is not free
+  std::map<std::array<int, 4>, FusedGeom> geom_cache;
+  void* fused = nullptr;  // FusedPlan (preprocess_fused.cu), owned by the plan: no process-global state
 };
 
 // Pillow precompute_coeffs + normalize_coeffs_8bpc (host, double precision).
@@ -55,10 +69,12 @@ int compute_axis_coeffs(int in_size, int out_size, std::vector<int32_t>& bounds,
                         std::vector<int32_t>& kk);
 
 // fused kernel (preprocess_fused.cu)
-bool fused_supported(const Plan& p, const ImgDesc& d, int* band_rows, size_t* smem_bytes);
+bool fused_supported(Plan& p, const ImgDesc& d, int* band_rows, size_t* smem_bytes);
 int fused_prepare(Plan& p);                                // after h_desc is final
 int fused_update_sources(const Plan& p, cudaStream_t s);   // after src/pitch changed
+// can image i of the plan take (src, pitch) without a new plan? (alignment class, staging size)
+bool fused_accepts(Plan& p, int i, const uint8_t* src, int pitch);
 int fused_launch(const Plan& p, void* dst, cudaStream_t stream);
-void fused_release(const Plan& p);
+void fused_release(Plan& p);
 
 }  // namespace tcb

@@ -21,6 +21,7 @@
 // HBM traffic is the source once (+ the band halo) and the output once.
 #include <algorithm>
 #include <array>
+#include <cmath>
 #include <cstdlib>
 #include <map>
 #include <type_traits>
@@ -110,21 +111,32 @@ __host__ __device__ __forceinline__ int p4_phys(int w) { return w; }
 // 0.522 ms on cfg3 against 0.552 ms for the double-buffered two-CTA version).
 template <int NW, int C, bool BIG>
 __global__ void __launch_bounds__(BIG ? 512 : 256, BIG ? 1 : 3)
-k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restrict__ work,
-                   const int32_t* __restrict__ pool, const uint8_t* __restrict__ lut,
-                   uint8_t* __restrict__ dst, int out_h, int out_w, int layout, int elem,
-                   int dst_aligned16) {
+k_preprocess_fused(const FusedDesc* __restrict__ descs, const int4* __restrict__ items,
+                   const int32_t* __restrict__ cta_first, const int32_t* __restrict__ pool,
+                   const uint8_t* __restrict__ lut, uint8_t* __restrict__ dst, int out_h, int out_w,
+                   int layout, int elem, int dst_aligned16) {
   extern __shared__ __align__(128) uint8_t smem[];
-  const int img = work[2 * blockIdx.x], yy0 = work[2 * blockIdx.x + 1];
-  const FusedDesc d = descs[img];
   const int tid = threadIdx.x, nthreads = blockDim.x;
-  const int yy1 = min(yy0 + d.band_rows, out_h);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t tma_phase = 0;  // parity of the next completion of bars[0]; runs on across work items
+  // Persistent CTA: the host cut the (image, output row) space of this launch into gridDim.x
+  // contiguous shares of equal estimated cost; a share is one to a few items (image, row span).
+  for (int item = cta_first[blockIdx.x]; item < cta_first[blockIdx.x + 1]; item++) {
+  const int4 wi = items[item];
+  const int img = wi.x, yy0 = wi.y;
+  const FusedDesc d = descs[img];
+  const int yy1 = wi.z;
   const int L = out_w * C;   // words per tmp4 slot = elements per output row
   const int ng = d.nwv + 1;  // ring slots
   const int wqp = d.wq;      // physical granules per P4 plane (padding included)
 
   // shared memory: barriers | raw stage | P4 | tmp4 ring
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
   uint8_t* raw = smem + 64;
   uint4* P4 = reinterpret_cast<uint4*>(raw + (size_t)d.stage_bytes);  // [C][wqp]
   uint32_t* tmp4 = reinterpret_cast<uint32_t*>(P4 + (size_t)C * wqp); // [ng][L]
@@ -145,12 +157,9 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
     tma_load_1d(raw + (size_t)s * d.stage_bytes, reinterpret_cast<const void*>(a0), bytes, &bars[s]);
   };
 
-  if (tid == 0) {
-    mbar_init(&bars[0], 1);
-    mbar_init(&bars[1], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
+  // Items of one CTA may belong to images of different sizes, i.e. different shared-memory
+  // layouts: nobody may still be reading the previous item's ring when this item's TMA lands.
+  if (item != cta_first[blockIdx.x]) __syncthreads();
   if (tid == 0) issue(0);
 
   // ---- per-thread constants ------------------------------------------------------------------------
@@ -306,16 +315,37 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
         uint32_t a[4][3];
 #pragma unroll
         for (int v = 0; v < 4; v++) { a[v][0] = 1u << (kPrecisionBits - 1); a[v][1] = 0; a[v][2] = 0; }
-        int slot = slot0;
-        for (int j = 0; j < d.nwv; j++) {
+        // tap words: unrolled for the common counts (the generic loop cost ~45 instructions per word)
+        const uint32_t* tbase = tmp4 + v_i0;
+        auto tap = [&](int j, int slot) {
           const uint4 kk = __ldg(vc + j);
           const uint32_t k0 = kk.x, k1 = kk.y, k2 = kk.z;
-          const uint4 px = *reinterpret_cast<const uint4*>(tmp4 + (size_t)slot * L + v_i0);
+          const uint4 px = *reinterpret_cast<const uint4*>(tbase + slot * L);
           a[0][0] = __dp4a(px.x, k0, a[0][0]); a[0][1] = __dp4a(px.x, k1, a[0][1]); a[0][2] = __dp4a(px.x, k2, a[0][2]);
           a[1][0] = __dp4a(px.y, k0, a[1][0]); a[1][1] = __dp4a(px.y, k1, a[1][1]); a[1][2] = __dp4a(px.y, k2, a[1][2]);
           a[2][0] = __dp4a(px.z, k0, a[2][0]); a[2][1] = __dp4a(px.z, k1, a[2][1]); a[2][2] = __dp4a(px.z, k2, a[2][2]);
           a[3][0] = __dp4a(px.w, k0, a[3][0]); a[3][1] = __dp4a(px.w, k1, a[3][1]); a[3][2] = __dp4a(px.w, k2, a[3][2]);
-          if (++slot == ng) slot = 0;
+        };
+        auto taps = [&](auto NWVc) {
+          constexpr int NWV = decltype(NWVc)::value;
+#pragma unroll
+          for (int j = 0; j < NWV; j++) {
+            int slot = slot0 + j;
+            if (slot >= ng) slot -= ng;
+            tap(j, slot);
+          }
+        };
+        switch (d.nwv) {
+          case 2: taps(std::integral_constant<int, 2>{}); break;
+          case 3: taps(std::integral_constant<int, 3>{}); break;
+          case 4: taps(std::integral_constant<int, 4>{}); break;
+          default: {
+            int slot = slot0;
+            for (int j = 0; j < d.nwv; j++) {
+              tap(j, slot);
+              if (++slot == ng) slot = 0;
+            }
+          }
         }
         uint32_t u[4];
 #pragma unroll
@@ -396,7 +426,8 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
   for (int i = 0; i <= n_groups; i++) {  // the last iteration only drains the vertical pass
     const int g = g_first + i;
     if (i < n_groups) {
-      mbar_wait(&bars[0], i & 1);
+      mbar_wait(&bars[0], tma_phase);
+      tma_phase ^= 1u;
       deinterleave(i);
       __syncthreads();  // raw stage drained, P4 complete
       if (tid == 0 && i + 1 < n_groups) issue(i + 1);
@@ -438,6 +469,7 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int32_t* __restric
       if (++slot == ng) slot = 0;
     }
   }
+  }  // work items of this CTA
 }
 
 // ---- host side ---------------------------------------------------------------------------------------
@@ -556,11 +588,6 @@ static int nw_class(int nw) {
   return -1;
 }
 
-struct FusedGeom {
-  int nw_class, nwv, wq, stage_bytes, threads;
-  size_t smem;
-};
-
 static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc& d, FusedGeom* g) {
   (void)elem;
   if (d.p1_axis != AXIS_H || d.p2_axis != AXIS_V) return false;
@@ -586,62 +613,100 @@ static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc&
   return g->smem <= kFusedMaxSmem;
 }
 
+struct FusedClass {
+  int threads = 256;
+  size_t smem = 0;                  // dynamic shared memory of the launch (max over the class's images)
+  std::vector<int> images;          // plan indices of the images this launch handles
+  std::vector<int4> items;          // (image, first output row, end output row, -)
+  std::vector<int32_t> cta_first;   // items of CTA b: [cta_first[b], cta_first[b + 1]), relative to items_off
+  size_t items_off = 0, cta_off = 0;
+};
+
 struct FusedPlan {
-  std::vector<FusedDesc> desc;                 // one per plan image (valid where fused)
-  std::map<int, std::vector<int32_t>> work;    // nw class -> (image, first output row) pairs
-  std::map<int, size_t> smem;                  // nw class -> dynamic shared memory
-  std::map<int, int> threads;
+  std::vector<FusedDesc> desc;      // one per plan image (valid where fused)
+  std::map<int, FusedClass> cls;    // nw class -> launch
   FusedDesc* d_desc = nullptr;
-  int32_t* d_work = nullptr;
-  std::map<int, size_t> work_off;
+  int4* d_items = nullptr;
+  int32_t* d_cta = nullptr;
   int32_t* d_pool = nullptr;
 };
 
-static std::map<const Plan*, FusedPlan*>& registry() {
-  static std::map<const Plan*, FusedPlan*> r;
-  return r;
+static FusedPlan* fused_of(const Plan& p) { return static_cast<FusedPlan*>(p.fused); }
+
+static const FusedGeom& cached_geometry(Plan& p, const ImgDesc& d) {
+  const std::array<int, 4> key = {d.W, d.H, d.cin, d.pitch};
+  auto it = p.geom_cache.find(key);
+  if (it == p.geom_cache.end()) {
+    FusedGeom g;
+    g.ok = fused_geometry(p.c, p.out_h, p.out_w, p.elem, d, &g);
+    it = p.geom_cache.emplace(key, g).first;
+  }
+  return it->second;
 }
 
-bool fused_supported(const Plan& p, const ImgDesc& d, int* band_rows, size_t* smem_bytes) {
-  FusedGeom g;
-  if (!fused_geometry(p.c, p.out_h, p.out_w, p.elem, d, &g)) return false;
-  // bands: enough CTAs to fill the GPU a few times over, but keep the halo overhead small
-  // (swept 4..24 CTAs per SM on cfg3: 6 is best, 0.556 ms; the curve is flat within 6 %)
-  const int sms = sm_count(p.device);
-  static const int per_sm = getenv("TCB_FUSED_CTAS_PER_SM") ? atoi(getenv("TCB_FUSED_CTAS_PER_SM")) : 6;
-  const long long target = (long long)per_sm * sms;
-  int rows = (int)std::min<long long>(p.out_h, std::max<long long>(8, ((long long)p.out_h * p.n + target - 1) / target));
-  const int nb = (p.out_h + rows - 1) / rows;
-  rows = (p.out_h + nb - 1) / nb;
-  *band_rows = rows;
+bool fused_supported(Plan& p, const ImgDesc& d, int* band_rows, size_t* smem_bytes) {
+  const FusedGeom& g = cached_geometry(p, d);
+  if (!g.ok) return false;
+  *band_rows = 0;  // the row spans are cut per launch, see partition_class()
   *smem_bytes = g.smem;
   return true;
 }
 
-template <int NW>
-static int launch_class(const Plan& p, const FusedPlan& fp, int cls, void* dst, cudaStream_t s) {
-  const auto it = fp.work.find(cls);
-  const int ctas = (int)(it->second.size() / 2);
-  const size_t smem = fp.smem.at(cls);
-  const int threads = fp.threads.at(cls);
-  const int32_t* work = fp.d_work + fp.work_off.at(cls);
-  const int al = (reinterpret_cast<uintptr_t>(dst) % 16 == 0) ? 1 : 0;
-#define TCB_FUSED(CC, BG)                                                                                 \
-  do {                                                                                                    \
-    TCB_CUDA(cudaFuncSetAttribute(k_preprocess_fused<NW, CC, BG>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                  (int)smem));                                                            \
-    k_preprocess_fused<NW, CC, BG><<<ctas, threads, smem, s>>>(fp.d_desc, work, fp.d_pool, p.d_lut,       \
-                                                               (uint8_t*)dst, p.out_h, p.out_w, p.layout, \
-                                                               p.elem, al);                               \
-  } while (0)
-  if (threads > 256) {
-    if (p.c == 3) TCB_FUSED(3, true); else TCB_FUSED(1, true);
-  } else {
-    if (p.c == 3) TCB_FUSED(3, false); else TCB_FUSED(1, false);
+// One template instance per (class, channels, CTA size); everything that needs the function
+// pointer (attributes, occupancy, launch) goes through this dispatcher.
+template <typename F>
+static int with_kernel(int cls, int c, bool big, F&& f) {
+#define TCB_K(NWv)                                                                         \
+  case NWv:                                                                                \
+    if (big) return c == 3 ? f(k_preprocess_fused<NWv, 3, true>) : f(k_preprocess_fused<NWv, 1, true>); \
+    return c == 3 ? f(k_preprocess_fused<NWv, 3, false>) : f(k_preprocess_fused<NWv, 1, false>);
+  switch (cls) {
+    TCB_K(2) TCB_K(3) TCB_K(4) TCB_K(5) TCB_K(6) TCB_K(8) TCB_K(10) TCB_K(12) TCB_K(16)
+    default: return set_error(TCB_ERR_INTERNAL, "bad coefficient class %d", cls);
   }
-#undef TCB_FUSED
-  count_launch();
-  return TCB_OK;
+#undef TCB_K
+}
+
+// Cuts the (image, output row) space of one launch into `ctas` contiguous shares of equal
+// estimated cost. A uniform batch such as cfg3 (256 x 1080p on 3 x 148 resident CTAs) used to run
+// as 1024 equal bands = 2.31 waves, the last one a third full; now every resident CTA gets exactly
+// one share and they all finish together. Cost model per output row of an image: its share of the
+// source bytes plus kOutCost byte-equivalents per output element (the vertical pass, table and
+// store; fitted to the per-resolution timings in DESIGN.md), which is what balances mixed batches.
+static void partition_class(const Plan& p, const FusedPlan& fp, FusedClass& fc, int ctas) {
+  constexpr double kOutCost = 14.0;
+  constexpr int kMinRows = 4;
+  const int out_h = p.out_h;
+  std::vector<double> row_cost(fc.images.size());
+  double total = 0;
+  for (size_t k = 0; k < fc.images.size(); k++) {
+    const FusedDesc& f = fp.desc[fc.images[k]];
+    row_cost[k] = (double)f.H * f.W * f.cin / out_h + kOutCost * p.out_w * p.c;
+    total += row_cost[k] * out_h;
+  }
+  const long long total_rows = (long long)fc.images.size() * out_h;
+  ctas = (int)std::max<long long>(1, std::min<long long>(ctas, total_rows / 8));
+  fc.items.clear();
+  fc.cta_first.assign(1, 0);
+  double cum = 0;
+  size_t k = 0;
+  int y = 0;
+  for (int b = 0; b < ctas; b++) {
+    const double target = b + 1 == ctas ? total * 2 : total * (b + 1) / ctas;
+    const size_t first_item = fc.items.size();
+    while (k < fc.images.size() && cum < target) {
+      const int left = out_h - y;
+      int take = (int)std::ceil((target - cum) / row_cost[k]);
+      if (take < kMinRows && fc.items.size() > first_item && y == 0) break;  // not worth a halo: next CTA
+      take = std::max(take, std::min(kMinRows, left));
+      if (left - take < kMinRows) take = left;  // no sliver for the next CTA either
+      fc.items.push_back(make_int4(fc.images[k], y, y + take, 0));
+      cum += row_cost[k] * take;
+      y += take;
+      if (y == out_h) { y = 0; k++; }
+    }
+    fc.cta_first.push_back((int32_t)fc.items.size());
+  }
 }
 
 int fused_prepare(Plan& p) {
@@ -654,11 +719,10 @@ int fused_prepare(Plan& p) {
   for (int i = 0; i < p.n; i++) {
     const ImgDesc& d = p.h_desc[i];
     if (!d.fused) continue;
-    FusedGeom g;
-    fused_geometry(p.c, p.out_h, p.out_w, p.elem, d, &g);
+    const FusedGeom g = cached_geometry(p, d);
     FusedDesc& f = fp->desc[i];
     f.src = d.src; f.W = d.W; f.H = d.H; f.pitch = d.pitch; f.cin = d.cin;
-    f.nw = g.nw_class; f.nwv = g.nwv; f.band_rows = d.band_rows; f.wq = g.wq;
+    f.nw = g.nw_class; f.nwv = g.nwv; f.band_rows = 0; f.wq = g.wq;
     f.stage_bytes = g.stage_bytes;
     f.aligned4 = (reinterpret_cast<uintptr_t>(d.src) % 4 == 0) && (d.pitch % 4 == 0);
     auto hk = std::make_pair(d.W, g.nw_class);
@@ -690,49 +754,82 @@ int fused_prepare(Plan& p) {
     }
     f.hc_off = htab[hk][0]; f.hw0_off = htab[hk][1]; f.hperm_off = htab[hk][2];
     f.vc_off = vtab[d.H][0]; f.vg_off = vtab[d.H][1]; f.vb_off = vtab[d.H][2];
-    auto& wl = fp->work[g.nw_class];
-    for (int y0 = 0; y0 < p.out_h; y0 += d.band_rows) { wl.push_back(i); wl.push_back(y0); }
-    fp->smem[g.nw_class] = std::max(fp->smem[g.nw_class], g.smem);
-    fp->threads[g.nw_class] = g.threads;
+    FusedClass& fc = fp->cls[g.nw_class];
+    fc.images.push_back(i);
+    fc.smem = std::max(fc.smem, g.smem);
+    fc.threads = g.threads;
   }
-  std::vector<int32_t> allwork;
-  for (auto& kv : fp->work) {
-    fp->work_off[kv.first] = allwork.size();
-    allwork.insert(allwork.end(), kv.second.begin(), kv.second.end());
+  // resident CTAs per launch, then the cost-balanced cut
+  static const int per_sm_cap = getenv("TCB_FUSED_CTAS_PER_SM") ? atoi(getenv("TCB_FUSED_CTAS_PER_SM")) : 0;
+  const int sms = sm_count(p.device);
+  std::vector<int4> allitems;
+  std::vector<int32_t> allcta;
+  for (auto& kv : fp->cls) {
+    FusedClass& fc = kv.second;
+    int per_sm = 0;
+    const int rc = with_kernel(kv.first, p.c, fc.threads > 256, [&](auto kern) -> int {
+      TCB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc.smem));
+      TCB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, fc.threads, fc.smem));
+      return TCB_OK;
+    });
+    if (rc) { delete fp; return rc; }
+    per_sm = std::max(per_sm, 1);
+    if (per_sm_cap > 0) per_sm = per_sm_cap;
+    partition_class(p, *fp, fc, per_sm * sms);
+    fc.items_off = allitems.size();
+    fc.cta_off = allcta.size();
+    allitems.insert(allitems.end(), fc.items.begin(), fc.items.end());
+    allcta.insert(allcta.end(), fc.cta_first.begin(), fc.cta_first.end());
   }
   if (pool.empty()) pool.push_back(0);
   cudaError_t e = cudaMalloc((void**)&fp->d_desc, sizeof(FusedDesc) * p.n);
   if (e == cudaSuccess) e = cudaMemcpy(fp->d_desc, fp->desc.data(), sizeof(FusedDesc) * p.n, cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) e = cudaMalloc((void**)&fp->d_work, allwork.size() * sizeof(int32_t));
-  if (e == cudaSuccess) e = cudaMemcpy(fp->d_work, allwork.data(), allwork.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&fp->d_items, allitems.size() * sizeof(int4));
+  if (e == cudaSuccess) e = cudaMemcpy(fp->d_items, allitems.data(), allitems.size() * sizeof(int4), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&fp->d_cta, allcta.size() * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemcpy(fp->d_cta, allcta.data(), allcta.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMalloc((void**)&fp->d_pool, pool.size() * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMemcpy(fp->d_pool, pool.data(), pool.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
-    cudaFree(fp->d_desc); cudaFree(fp->d_work); cudaFree(fp->d_pool);
+    cudaFree(fp->d_desc); cudaFree(fp->d_items); cudaFree(fp->d_cta); cudaFree(fp->d_pool);
     delete fp;
     return set_error(TCB_ERR_NOMEM, "fused preprocess set-up failed: %s", cudaGetErrorString(e));
   }
-  registry()[&p] = fp;
+  p.fused = fp;
   return TCB_OK;
 }
 
-void fused_release(const Plan& p) {
-  auto it = registry().find(&p);
-  if (it == registry().end()) return;
-  cudaFree(it->second->d_desc); cudaFree(it->second->d_work); cudaFree(it->second->d_pool);
-  delete it->second;
-  registry().erase(it);
+void fused_release(Plan& p) {
+  FusedPlan* fp = fused_of(p);
+  if (!fp) return;
+  cudaFree(fp->d_desc); cudaFree(fp->d_items); cudaFree(fp->d_cta); cudaFree(fp->d_pool);
+  delete fp;
+  p.fused = nullptr;
+}
+
+// A run may hand the plan new source pointers / pitches. The launch geometry (class, shared
+// memory) was fixed at creation, so the new pitch must still fit the class's staging area; the
+// row-alignment flag and the staging size are per image and simply follow.
+bool fused_accepts(Plan& p, int i, const uint8_t* src, int pitch) {
+  const FusedPlan* fp = fused_of(p);
+  if (!fp) return false;
+  ImgDesc t = p.h_desc[i];
+  t.src = src; t.pitch = pitch;
+  const FusedGeom g = cached_geometry(p, t);
+  if (!g.ok) return false;
+  const auto it = fp->cls.find(g.nw_class);
+  return it != fp->cls.end() && g.nw_class == fp->desc[i].nw && g.smem <= it->second.smem;
 }
 
 int fused_update_sources(const Plan& p, cudaStream_t s) {
-  auto it = registry().find(&p);
-  if (it == registry().end()) return TCB_OK;
-  FusedPlan* fp = it->second;
+  FusedPlan* fp = fused_of(p);
+  if (!fp) return TCB_OK;
   for (int i = 0; i < p.n; i++)
     if (p.h_desc[i].fused) {
       FusedDesc& f = fp->desc[i];
       f.src = p.h_desc[i].src;
       f.pitch = p.h_desc[i].pitch;
+      f.stage_bytes = (int)round_up((uint64_t)4 * f.pitch + 48, 128);  // follows the pitch (fused_accepts checked the fit)
       f.aligned4 = (reinterpret_cast<uintptr_t>(f.src) % 4 == 0) && (f.pitch % 4 == 0);  // may change from run to run
     }
   TCB_CUDA(cudaMemcpyAsync(fp->d_desc, fp->desc.data(), sizeof(FusedDesc) * p.n, cudaMemcpyHostToDevice, s));
@@ -740,24 +837,20 @@ int fused_update_sources(const Plan& p, cudaStream_t s) {
 }
 
 int fused_launch(const Plan& p, void* dst, cudaStream_t s) {
-  auto it = registry().find(&p);
-  if (it == registry().end()) return set_error(TCB_ERR_INTERNAL, "fused plan missing");
-  const FusedPlan& fp = *it->second;
-  for (auto& kv : fp.work) {
-    int rc = TCB_OK;
-    switch (kv.first) {
-      case 2: rc = launch_class<2>(p, fp, 2, dst, s); break;
-      case 3: rc = launch_class<3>(p, fp, 3, dst, s); break;
-      case 4: rc = launch_class<4>(p, fp, 4, dst, s); break;
-      case 5: rc = launch_class<5>(p, fp, 5, dst, s); break;
-      case 6: rc = launch_class<6>(p, fp, 6, dst, s); break;
-      case 10: rc = launch_class<10>(p, fp, 10, dst, s); break;
-      case 8: rc = launch_class<8>(p, fp, 8, dst, s); break;
-      case 12: rc = launch_class<12>(p, fp, 12, dst, s); break;
-      case 16: rc = launch_class<16>(p, fp, 16, dst, s); break;
-      default: rc = set_error(TCB_ERR_INTERNAL, "bad coefficient class %d", kv.first);
-    }
+  const FusedPlan* fp = fused_of(p);
+  if (!fp) return set_error(TCB_ERR_INTERNAL, "fused plan missing");
+  const int al = (reinterpret_cast<uintptr_t>(dst) % 16 == 0) ? 1 : 0;
+  for (auto& kv : fp->cls) {
+    const FusedClass& fc = kv.second;
+    const int ctas = (int)fc.cta_first.size() - 1;
+    const int rc = with_kernel(kv.first, p.c, fc.threads > 256, [&](auto kern) -> int {
+      kern<<<ctas, fc.threads, fc.smem, s>>>(fp->d_desc, fp->d_items + fc.items_off, fp->d_cta + fc.cta_off,
+                                            fp->d_pool, p.d_lut, (uint8_t*)dst, p.out_h, p.out_w, p.layout,
+                                            p.elem, al);
+      return TCB_OK;
+    });
     if (rc) return rc;
+    count_launch();
   }
   return TCB_OK;
 }

@@ -95,6 +95,9 @@ int TcbRegionSet(void* region, uint64_t offset, const void* src, uint64_t byte_s
   if (byte_size == 0) return TCB_OK;
   TCB_CHECK_ARG(src != nullptr, "TcbRegionSet: src is NULL");
   TCB_DEVICE_GUARD(r->device);
+  if (tcb::staging_applies(src, byte_size))  // pageable numpy memory: pinned ring + parallel memcpy
+    return tcb::staged_h2d(r->device, static_cast<char*>(r->base) + offset, src, byte_size,
+                           static_cast<cudaStream_t>(stream));
   TCB_CUDA(cudaMemcpyAsync(static_cast<char*>(r->base) + offset, src, byte_size, cudaMemcpyDefault,
                            static_cast<cudaStream_t>(stream)));
   return TCB_OK;
@@ -111,6 +114,9 @@ int TcbRegionGet(void* region, uint64_t offset, void* dst, uint64_t byte_size, v
   TCB_DEVICE_GUARD(r->device);
   if (byte_size > 0) {
     TCB_CHECK_ARG(dst != nullptr, "TcbRegionGet: dst is NULL");
+    if (tcb::staging_applies(dst, byte_size))
+      return tcb::staged_d2h(r->device, dst, static_cast<char*>(r->base) + offset, byte_size,
+                             static_cast<cudaStream_t>(stream));
     TCB_CUDA(cudaMemcpyAsync(dst, static_cast<char*>(r->base) + offset, byte_size,
                              cudaMemcpyDefault, static_cast<cudaStream_t>(stream)));
   }
@@ -191,7 +197,15 @@ int TcbMemcpy(int device_id, void* dst, const void* src, uint64_t byte_size, voi
   TCB_DEVICE_GUARD(device_id);
   if (byte_size > 0) {
     TCB_CHECK_ARG(dst != nullptr && src != nullptr, "TcbMemcpy: NULL pointer");
-    TCB_CUDA(cudaMemcpyAsync(dst, src, byte_size, cudaMemcpyDefault, static_cast<cudaStream_t>(stream)));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (tcb::staging_applies(src, byte_size) && tcb::is_device_ptr(dst)) {
+      const int rc = tcb::staged_h2d(device_id, dst, src, byte_size, s);
+      if (rc) return rc;
+    } else if (tcb::staging_applies(dst, byte_size) && tcb::is_device_ptr(src)) {
+      return tcb::staged_d2h(device_id, dst, src, byte_size, s);  // returns with dst complete
+    } else {
+      TCB_CUDA(cudaMemcpyAsync(dst, src, byte_size, cudaMemcpyDefault, s));
+    }
   }
   if (sync) TCB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
   return TCB_OK;

@@ -15,7 +15,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from ._device import current_device, device_buffer, stream_ptr, to_device_u8, to_host
+from ._device import current_device, device_buffer, stream_ptr, to_host
 from .utils import triton_to_np_dtype
 
 FORMAT_NONE, FORMAT_NHWC, FORMAT_NCHW = 0, 1, 2  # model_config.proto ModelInput.Format
@@ -208,6 +208,54 @@ class HostBatchPipeline:
         cur.wait_stream(self.s_in)
         cur.wait_stream(self.s_out)
 
+    def run_pageable(self, images, dst_ptr, dst_capacity, host_out=None):
+        """Same pipeline from ordinary (pageable) host memory, which is what the reference API
+        starts from: ``images`` is a uint8 ndarray [n, H, W, C]. Each piece is first copied by the
+        CPU into one of two pinned staging buffers (allocated on first use) while the previous
+        piece's DMA and kernel run; ``host_out`` (ndarray or None) receives the result."""
+        import torch
+
+        if dst_capacity < self.n * self.out_bytes_per_image:
+            raise ValueError("destination holds %d bytes, the batch needs %d"
+                             % (dst_capacity, self.n * self.out_bytes_per_image))
+        flat = images.reshape(-1)
+        if flat.dtype != np.uint8 or flat.size != self.n * self.img_bytes:
+            raise ValueError("images must be uint8 with %d bytes in total" % (self.n * self.img_bytes))
+        piece = max(self.bounds[k + 1] - self.bounds[k] for k in range(len(self.plans))) * self.img_bytes
+        if getattr(self, "_pin", None) is None:
+            self._pin = [torch.empty(piece, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+            self._pin_np = [t.numpy() for t in self._pin]
+            self._pin_free = [torch.cuda.Event() for _ in range(2)]
+            self._pin_out = torch.empty(self.n * self.out_bytes_per_image, dtype=torch.uint8, pin_memory=True)
+        cur = torch.cuda.current_stream(self.device)
+        self.s_in.wait_stream(cur)
+        self.s_out.wait_stream(cur)
+        base = self.stage.data_ptr()
+        for k, plan in enumerate(self.plans):
+            i0, i1 = self.bounds[k], self.bounds[k + 1]
+            nb = (i1 - i0) * self.img_bytes
+            b = k & 1
+            if k >= 2:
+                self._pin_free[b].synchronize()  # the DMA that last read this staging buffer is done
+            np.copyto(self._pin_np[b][:nb], flat[i0 * self.img_bytes:i1 * self.img_bytes])
+            _lib.check(_lib.lib.TcbMemcpy(self.device, base + i0 * self.img_bytes, self._pin[b].data_ptr(), nb,
+                                          self.s_in.cuda_stream, 0))
+            self._pin_free[b].record(self.s_in)
+            self.events[k].record(self.s_in)
+            self.s_out.wait_event(self.events[k])
+            ob = (i1 - i0) * self.out_bytes_per_image
+            plan.run([base + i * self.img_bytes for i in range(i0, i1)], int(dst_ptr) + i0 * self.out_bytes_per_image,
+                     ob, stream=self.s_out.cuda_stream)
+            if host_out is not None:
+                _lib.check(_lib.lib.TcbMemcpy(self.device, self._pin_out.data_ptr() + i0 * self.out_bytes_per_image,
+                                              int(dst_ptr) + i0 * self.out_bytes_per_image, ob,
+                                              self.s_out.cuda_stream, 0))
+        cur.wait_stream(self.s_in)
+        cur.wait_stream(self.s_out)
+        if host_out is not None:
+            cur.synchronize()
+            np.copyto(host_out.reshape(-1).view(np.uint8), self._pin_out.numpy())
+
     def close(self):
         for p in self.plans:
             p.close()
@@ -233,20 +281,25 @@ _plan_cache = {}
 def preprocess(img, format, dtype, c, h, w, scaling, protocol=None):
     """Pre-process one PIL image to the size, type and format requirements given (same contract
     as the reference's ``preprocess``); returns a numpy array shaped (c, h, w) for FORMAT_NCHW,
-    else (h, w, c)."""
+    else (h, w, c). The plan and its two device buffers are kept per (device, geometry, dtype,
+    scaling), so a repeated call costs one H2D copy, one kernel and one D2H copy."""
     c, h, w = int(c), int(h), int(w)
     src = _pil_to_array(img, c)
     dev = current_device()
     H, W, cin = src.shape
     key = (dev, W, H, cin, format == FORMAT_NCHW, dtype, c, h, w, scaling)
-    plan = _plan_cache.get(key)
-    if plan is None:
+    entry = _plan_cache.get(key)
+    if entry is None:
         if len(_plan_cache) > 64:
+            for old in _plan_cache.values():
+                old[0].close()
             _plan_cache.clear()
         plan = PreprocessPlan([(W, H, cin)], format, dtype, c, h, w, scaling, device=dev)
-        _plan_cache[key] = plan
-    d_src = to_device_u8(src, dev)
-    d_out = device_buffer(plan.out_bytes_per_image, dev)
-    plan.run([d_src.data_ptr()], d_out.data_ptr(), plan.out_bytes_per_image)
+        entry = (plan, device_buffer(src.size, dev), device_buffer(plan.out_bytes_per_image, dev))
+        _plan_cache[key] = entry
+    plan, d_src, d_out = entry
+    s = stream_ptr(dev)
+    _lib.check(_lib.lib.TcbMemcpy(dev, d_src.data_ptr(), src.ctypes.data, src.size, s, 0))
+    plan.run([d_src.data_ptr()], d_out.data_ptr(), plan.out_bytes_per_image, stream=s)
     host = to_host(d_out.data_ptr(), plan.out_bytes_per_image, dev)  # synchronises
     return host.view(plan.out_dtype).reshape(plan.out_shape[1:])

@@ -259,3 +259,87 @@ def deserialize_bytes_tensor(encoded_tensor):
     h_off = to_host(offsets.data_ptr(), offsets.numel() * 8, dev).view(np.int64)
     h_pay = to_host(payload.data_ptr(), payload.numel(), dev)
     return _object_array_from(h_off, h_pay)
+
+
+# ---- BF16 (utils/__init__.py:279-348 of the reference) ---------------------------------------
+
+
+def serialize_bf16_to_device(values, out=None, out_offset=0, device=None, sync=True):
+    """Pack a device-resident float32 tensor into bfloat16 wire bytes (upper 16 bits of every
+    float32 pattern, C order). ``values``: contiguous torch float32 CUDA tensor; ``out``: None (a new
+    torch uint8 tensor), a torch CUDA tensor or a ``CudaSharedMemoryRegion``, written from
+    ``out_offset``. Returns (out, bytes_written)."""
+    import torch
+
+    if values.dtype != torch.float32:
+        raise_error("cannot serialize bf16 tensor: invalid datatype")
+    if not values.is_contiguous():
+        raise ValueError("serialize_bf16_to_device needs a C-contiguous tensor")
+    dev = values.device.index if device is None else device
+    n = int(values.numel())
+    if out is None:
+        out = torch.empty(2 * n, dtype=torch.uint8, device="cuda:%d" % dev)
+    dst_ptr, dst_cap = _dst_of(out, out_offset)
+    _lib.check(_lib.lib.TcbBf16Serialize(dev, values.data_ptr(), n, dst_ptr, dst_cap, stream_ptr(dev)))
+    if sync:
+        _lib.check(_lib.lib.TcbStreamSync(dev, stream_ptr(dev)))
+    return out, 2 * n
+
+
+def deserialize_bf16_from_device(stream, nbytes=None, stream_offset=0, out=None, device=None, sync=True):
+    """Expand bfloat16 wire bytes that live on the device (torch uint8 CUDA tensor or a
+    ``CudaSharedMemoryRegion``) into a torch float32 CUDA tensor of ``nbytes // 2`` values."""
+    import torch
+
+    src_ptr, cap = _dst_of(stream, stream_offset)
+    dev = _device_of(stream) if device is None else device
+    nbytes = cap if nbytes is None else int(nbytes)
+    if nbytes > cap:
+        raise ValueError("stream of %d bytes exceeds the buffer (%d)" % (nbytes, cap))
+    if out is None:
+        out = torch.empty(nbytes // 2, dtype=torch.float32, device="cuda:%d" % dev)
+    rc = _lib.lib.TcbBf16Deserialize(dev, src_ptr, nbytes, out.data_ptr(), out.numel() * 4, stream_ptr(dev))
+    if rc == _lib.TCB_ERR_TRUNCATED:
+        raise struct.error(_lib.last_error())
+    _lib.check(rc)
+    if sync:
+        _lib.check(_lib.lib.TcbStreamSync(dev, stream_ptr(dev)))
+    return out
+
+
+def serialize_bf16_tensor(input_tensor):
+    """Same contract as the reference (utils/__init__.py:279-323): a float32 ndarray in, a 0-d
+    ``np.object_`` array holding the 2-bytes-per-element wire ``bytes`` out (empty input:
+    ``np.empty([0], dtype=np.object_)``). Logical C order, so views and Fortran arrays work."""
+    import torch
+
+    if input_tensor.size == 0:
+        return np.empty([0], dtype=np.object_)
+    if input_tensor.dtype != np.float32:
+        raise_error("cannot serialize bf16 tensor: invalid datatype")
+    dev = current_device()
+    d_src = to_device_u8(np.ascontiguousarray(input_tensor), dev)
+    n = int(input_tensor.size)
+    out = torch.empty(2 * n, dtype=torch.uint8, device="cuda:%d" % dev)
+    _lib.check(_lib.lib.TcbBf16Serialize(dev, d_src.data_ptr(), n, out.data_ptr(), 2 * n, stream_ptr(dev)))
+    flattened = to_host(out.data_ptr(), 2 * n, dev).tobytes()  # synchronises
+    return np.asarray(flattened, dtype=np.object_)
+
+
+def deserialize_bf16_tensor(encoded_tensor):
+    """Same contract as the reference (utils/__init__.py:326-348), including its result shape:
+    the reference appends 1-tuples from ``struct.unpack``, so n values come back as a float32
+    array shaped (n, 1) (an empty buffer as shape (0,)); an odd trailing byte raises
+    ``struct.error``."""
+    buf = memoryview(encoded_tensor).cast("B") if not isinstance(encoded_tensor, (bytes, bytearray)) \
+        else encoded_tensor
+    if len(buf) == 0:
+        return np.array([], dtype=np.float32)
+    if len(buf) & 1:
+        raise struct.error("unpack_from requires a buffer of at least %d bytes for unpacking 2 bytes at offset %d "
+                           "(actual buffer size is %d)" % (len(buf) + 1, len(buf) - 1, len(buf)))
+    dev = current_device()
+    d_stream = to_device_u8(buf, dev)
+    out = deserialize_bf16_from_device(d_stream, len(buf), 0, None, dev, sync=False)
+    host = to_host(out.data_ptr(), out.numel() * 4, dev).view(np.float32)
+    return host.reshape(-1, 1)
