@@ -140,3 +140,27 @@ def test_bytes_contents_quirks_and_garbage_tail():
     with pytest.raises(struct.error):
         cudashm.get_contents_as_numpy(h2, np.object_, [7])  # one more element than the region holds
     cudashm.destroy_shared_memory_region(h2)
+
+
+@pytest.mark.parametrize("nbytes", [2 * 1024 * 1024, 4 * 1024 * 1024 + 17, 37 * 1024 * 1024 + 5])
+def test_large_pageable_copies_go_through_the_staging_ring_and_round_trip(nbytes):
+    """set/get of arrays above the staging threshold (staging.cu: pinned ring + host copy threads):
+    bytes must survive both directions, at an offset, with neighbours untouched."""
+    torch, utils, cudashm = _mods()
+    rng = np.random.default_rng(nbytes)
+    a = rng.integers(0, 256, nbytes, dtype=np.uint8)
+    region = cudashm.create_shared_memory_region("staged", nbytes + 64, 0)
+    try:
+        guard = np.full(nbytes + 64, 0xEE, dtype=np.uint8)
+        cudashm.set_shared_memory_region(region, [guard])
+        cudashm.set_shared_memory_region(region, [a], offset=32)
+        back = cudashm.get_contents_as_numpy(region, np.uint8, [nbytes + 64])
+        assert np.array_equal(back[32:32 + nbytes], a)
+        assert (back[:32] == 0xEE).all() and (back[32 + nbytes:] == 0xEE).all()
+        # typed view, two arrays back to back (the reference's packing)
+        f = rng.standard_normal(nbytes // 8).astype(np.float32)
+        cudashm.set_shared_memory_region(region, [f, f[::-1].copy()])
+        got = cudashm.get_contents_as_numpy(region, np.float32, [2, f.size])
+        assert np.array_equal(got[0], f) and np.array_equal(got[1], f[::-1])
+    finally:
+        cudashm.destroy_shared_memory_region(region)

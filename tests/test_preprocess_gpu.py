@@ -352,3 +352,107 @@ def test_host_batch_pipeline_matches_oracle(chunks):
     finally:
         pipe.close()
         cudashm.destroy_shared_memory_region(region)
+
+
+def test_plan_run_with_changed_pitch_and_failed_run_keeps_plan_consistent():
+    """(1) a run may raise an image's pitch - the staging size must follow and the
+    result stay exact; (2) a pitch the launch cannot hold is refused; (3) a run that fails
+    validation half-way must not leave stale pointers behind."""
+    import ctypes
+
+    import torch
+
+    from triton_client_b200 import _lib
+
+    rng = np.random.default_rng(31)
+    shapes = [(480, 640), (300, 600)]  # (H, W): same coefficient class (one launch), different staging sizes
+    srcs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in shapes]
+    lut = pb.scaling_lut("FP32", 3, "INCEPTION")
+    lut_c = np.ascontiguousarray(lut)
+
+    def padded(a, pitch):
+        h, w, _ = a.shape
+        buf = torch.zeros((h, pitch), dtype=torch.uint8, device="cuda")
+        buf[:, : w * 3] = torch.from_numpy(a.reshape(h, w * 3)).cuda()
+        return buf
+
+    def images(bufs, pitches):
+        arr = (_lib.TcbImage * 2)()
+        for i, (b, p) in enumerate(zip(bufs, pitches)):
+            arr[i] = _lib.TcbImage(b.data_ptr(), shapes[i][1], shapes[i][0], p, 3)
+        return arr
+
+    p0 = [640 * 3, 600 * 3]
+    bufs0 = [padded(a, p) for a, p in zip(srcs, p0)]
+    plan = ctypes.c_void_p()
+    _lib.check(_lib.lib.TcbPreprocessPlanCreate(0, images(bufs0, p0), 2, 3, 224, 224, _lib.LAYOUT_NCHW,
+                                                lut_c.ctypes.data, 4, 2, ctypes.byref(plan)))
+    out = torch.zeros((2, 3, 224, 224), dtype=torch.float32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    want = [oracle_preprocess(a, 3, 224, 224, 2, "FP32", "INCEPTION") for a in srcs]
+
+    def run(imgs):
+        out.zero_()
+        rc = _lib.lib.TcbPreprocessPlanRun(plan, imgs, out.data_ptr(), out.numel() * 4, stream)
+        torch.cuda.synchronize()
+        return rc
+
+    assert run(None) == 0
+    for i in range(2):
+        assert np.array_equal(out[i].cpu().numpy(), want[i])
+    # (1) the SMALLER image's pitch grows (still below the larger image's): accepted and exact
+    p1 = [640 * 3, 600 * 3 + 100]
+    bufs1 = [bufs0[0], padded(srcs[1], p1[1])]
+    assert run(images(bufs1, p1)) == 0
+    for i in range(2):
+        assert np.array_equal(out[i].cpu().numpy(), want[i])
+    # odd pitch: rows lose their 4-byte alignment, still exact
+    p2 = [640 * 3 + 1, 600 * 3 + 3]
+    bufs2 = [padded(a, p) for a, p in zip(srcs, p2)]
+    assert run(images(bufs2, p2)) == 0
+    for i in range(2):
+        assert np.array_equal(out[i].cpu().numpy(), want[i])
+    # (2) a pitch far beyond what the launch's shared memory was sized for is refused
+    p3 = [640 * 3 + 1, 65536]
+    bufs3 = [bufs2[0], padded(srcs[1], p3[1])]
+    assert run(images(bufs3, p3)) == _lib.TCB_ERR_UNSUPPORTED
+    # (3) ... and that failed run committed nothing: the plan still runs on the previous sources
+    assert run(None) == 0
+    for i in range(2):
+        assert np.array_equal(out[i].cpu().numpy(), want[i])
+    # geometry mismatch on image 1 after a changed pointer on image 0: nothing of it sticks either
+    bad = images([bufs0[0], bufs0[1]], p0)
+    bad[1].width = 601
+    assert run(bad) == _lib.TCB_ERR_INVALID_ARG
+    del bufs0  # image 0's "new" pointer from the failed call dies here; the plan must not use it
+    torch.cuda.empty_cache()
+    assert run(None) == 0
+    for i in range(2):
+        assert np.array_equal(out[i].cpu().numpy(), want[i])
+    _lib.lib.TcbPreprocessPlanDestroy(plan)
+
+
+def test_large_mixed_batch_every_image_exact():
+    """600 images of the cfg5 menu in one plan: exercises the cost-balanced work partition (items
+    that start and end in the middle of images, CTAs whose share spans images of different sizes)
+    and checks EVERY image against the oracle."""
+    import torch
+
+    from triton_client_b200.image_client import preprocess_batch
+
+    menu = [(640, 480), (800, 600), (1024, 768), (1280, 720), (1920, 1080), (500, 375), (375, 500), (224, 224), (150, 100)]
+    rng = np.random.default_rng(77)
+    idx = rng.choice(len(menu), size=600)
+    base = {}
+    for k, (w, h) in enumerate(menu):  # a few distinct images per size, reused
+        base[k] = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for _ in range(3)]
+    pick = rng.integers(0, 3, size=600)
+    d_base = {k: [torch.from_numpy(a).cuda() for a in v] for k, v in base.items()}
+    imgs = [d_base[int(i)][int(j)] for i, j in zip(idx, pick)]
+    for fmt, dt, sc in ((1, "FP16", "INCEPTION"), (2, "FP32", "VGG")):
+        out, plan = preprocess_batch(imgs, fmt, dt, 3, 224, 224, sc)
+        host = out.cpu().numpy()
+        want = {(k, j): oracle_preprocess(base[k][j], 3, 224, 224, fmt, dt, sc) for k in base for j in range(3)}
+        for n, (i, j) in enumerate(zip(idx, pick)):
+            assert np.array_equal(host[n], want[(int(i), int(j))]), (n, menu[int(i)], fmt, dt)
+        plan.close()

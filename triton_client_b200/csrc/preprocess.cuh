@@ -35,6 +35,7 @@ struct ImgDesc {
 // launch geometry of one image in the fused kernel (preprocess_fused.cu)
 struct FusedGeom {
   int nw_class = 0, nwv = 0, wq = 0, stage_bytes = 0, threads = 0;
+  int mma_nk = 0, mma_wp = 0;  // IMMA variant (nw_class >= 100): k-steps per tile, bytes per planar line
   size_t smem = 0;
   bool ok = false;
 };

@@ -86,6 +86,11 @@ struct FusedDesc {
   int32_t wq;        // words per planar row incl. padding
   int32_t stage_bytes;
   int32_t aligned4;  // rows start 4-byte aligned: the de-interleave reads them without funnel shifts
+  // IMMA variant (k_preprocess_fused_mma), valid when mma_nk > 0
+  int32_t mma_nk;     // 32-pixel k-steps per tile of 8 output columns
+  int32_t mma_wp;     // bytes per planar line in shared memory (multiple of 16, == 16 mod 128)
+  int32_t mma_b_off;  // pool: B fragments [n-tile][k-step][plane][lane][2]
+  int32_t mma_s_off;  // pool: first source pixel of every n-tile's window [n-tiles] (multiple of 16)
 };
 
 __device__ __forceinline__ uint32_t fetch_conv(const uint8_t* row, int cin, int C, int x, int ch) {
@@ -472,6 +477,347 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int4* __restrict__
   }  // work items of this CTA
 }
 
+// =====================================================================================================
+// IMMA variant of the fused kernel (RGB -> RGB, rows 16-byte aligned).
+//
+// The horizontal pass is a banded u8 GEMM: tmp[line][xx] = sum_x P[line][x] * k[x][xx], exact in
+// s32 when the 22-bit coefficient is split into three byte planes (k = k0 + k1*2^8 + k2*2^16), which
+// is what the dp4a kernel above already does one lane at a time. Here a warp does it with
+// mma.sync.m16n8k32 (u8 x u8 -> s32, SASS IMMA.16832.U8.U8): A = 16 lines x 32 source pixels from
+// shared memory via ldmatrix, B = 32 pixels x 8 output columns of one coefficient plane, resident in
+// registers for the two 8-column tiles every warp owns. One 8-column tile sees a window of NK*32
+// source pixels (NK <= 3 for scales up to ~8.6), so a tile costs NK*3 IMMAs per 16 lines instead of
+// 8 columns x 16 lines x NK*8... dp4a lane-instructions: about a fifth of the issue slots.
+//
+// Rows stream through the CTA eight at a time (two 4-row groups = two words of the tmp4 ring):
+//   wait TMA(s) | de-interleave raw -> planar lines P[slot][x] (LDS.128, PRMT, STS.128) | barrier |
+//   start TMA(s+1) | IMMA pass P -> tmp4 ring | barrier | vertical pass (dp4a) + table + store.
+// Lines: slot = r*6 + ch*2 + half holds row 4*half + r of the step, channel ch. A 16-line MMA tile t
+// is rows r = 2t, 2t+1 of all six (ch, half) pairs (+ 2 pad lines that alias pair 0, 1), so thread
+// (g = lane/4) ends up with the four rows of pair g for two adjacent columns: exactly one tmp4 word
+// each, packed with PRMT, no shuffles.
+// =====================================================================================================
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void imma_16832(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+      : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void imma_16832_first(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+      : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(0));
+}
+
+constexpr int kMmaTilesPerWarp = 2;
+constexpr int kMmaLines = 24;  // 4 rows x 3 channels x 2 halves
+
+template <int NK, int WMAX>
+__global__ void __launch_bounds__(WMAX * 32, WMAX <= 16 ? 2 : 1)
+k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restrict__ items,
+                       const int32_t* __restrict__ cta_first, const int32_t* __restrict__ pool,
+                       const uint8_t* __restrict__ lut, uint8_t* __restrict__ dst, int out_h, int out_w,
+                       int layout, int elem, int dst_aligned16) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr int C = 3;
+  const int tid = threadIdx.x, nthreads = blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, tig = lane & 3;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t tma_phase = 0;
+  const bool nchw = layout == TCB_LAYOUT_NCHW;
+  const int L = out_w * C;
+  const int ntiles = (out_w + 7) >> 3;
+  // ---- vertical-pass constants (depend on the launch only) ---------------------------------------
+  const bool vec4 = dst_aligned16 && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));
+  const int upl = nchw ? out_w / 4 : L / 4;       // units (4 consecutive output elements) per line
+  const int n_units = vec4 ? (nchw ? C * upl : upl) : 0;
+  const int vb_rows = n_units > 0 ? max(1, nthreads / n_units) : 1;  // output rows handled side by side
+  const int vk = n_units > 0 ? tid / n_units : 0;
+  const int vu0 = n_units > 0 ? tid - vk * n_units : 0;
+  // ---- horizontal-pass constants --------------------------------------------------------------------
+  // accumulator ownership: lines g, g+8 of both tiles = rows 0..3 of pair g = (channel g>>1, half g&1)
+  const int own_ch = g >> 1, own_half = g & 1;
+  const bool own = g < 6;
+
+  for (int item = cta_first[blockIdx.x]; item < cta_first[blockIdx.x + 1]; item++) {
+    const int4 wi = items[item];
+    const int img = wi.x, yy0 = wi.y, yy1 = wi.z;
+    const FusedDesc d = descs[img];
+    const int ng = d.nwv + 1;
+    const int Wp = d.mma_wp;
+    // shared memory: barrier | raw stage (8 rows) | P lines | tmp4 ring
+    uint8_t* raw = smem + 128;
+    uint8_t* P = raw + d.stage_bytes;
+    uint32_t* tmp4 = reinterpret_cast<uint32_t*>(P + (size_t)kMmaLines * Wp);
+    const uint32_t P_s = smem_u32(P);
+
+    const int32_t* vb = pool + d.vb_off;
+    const int32_t* vg = pool + d.vg_off;
+    const int ys = vb[2 * yy0], ye = vb[2 * (yy1 - 1)] + vb[2 * (yy1 - 1) + 1];  // source rows [ys, ye)
+    const int s_first = ys >> 3, s_last = (ye - 1) >> 3;
+
+    auto issue = [&](int s) {  // thread 0: rows [8s, min(8s + 8, H)) -> raw stage
+      const int r0 = 8 * s, r1 = min(r0 + 8, d.H);
+      const uint8_t* a0 = d.src + (size_t)r0 * d.pitch;
+      const uint32_t bytes = (uint32_t)((r1 - r0 - 1) * d.pitch + ((d.W * 3 + 15) & ~15));
+      mbar_expect_tx(&bars[0], bytes);
+      tma_load_1d(raw, a0, bytes, &bars[0]);
+    };
+    // different images = different shared-memory layouts: see k_preprocess_fused
+    if (item != cta_first[blockIdx.x]) __syncthreads();
+    if (tid == 0) issue(s_first);
+
+    // ---- per-item constants ---------------------------------------------------------------------
+    // B fragments of this warp's two tiles
+    uint32_t bfr[kMmaTilesPerWarp][NK][3][2];
+    int s_nt[kMmaTilesPerWarp];
+#pragma unroll
+    for (int q = 0; q < kMmaTilesPerWarp; q++) {
+      const int nt = warp * kMmaTilesPerWarp + q;
+      s_nt[q] = 0;
+#pragma unroll
+      for (int ks = 0; ks < NK; ks++)
+#pragma unroll
+        for (int p = 0; p < 3; p++) { bfr[q][ks][p][0] = 0; bfr[q][ks][p][1] = 0; }
+      if (nt < ntiles) {
+        s_nt[q] = pool[d.mma_s_off + nt];
+        const uint2* bp = reinterpret_cast<const uint2*>(pool + d.mma_b_off) + (size_t)nt * NK * 3 * 32 + lane;
+#pragma unroll
+        for (int ks = 0; ks < NK; ks++)
+#pragma unroll
+          for (int p = 0; p < 3; p++) {
+            const uint2 v = __ldg(bp + (ks * 3 + p) * 32);
+            bfr[q][ks][p][0] = v.x; bfr[q][ks][p][1] = v.y;
+          }
+      }
+    }
+    // ldmatrix row address of this lane for tile t: matrix mi = lane >> 3 -> rows (mi & 1) * 8 .., k half mi >> 1
+    uint32_t a_addr[2];
+    {
+      const int mi = lane >> 3, rr = lane & 7;
+      const int jj = rr < 6 ? rr : rr - 6;  // pad lines alias pairs 0 and 1 (results unused)
+#pragma unroll
+      for (int t = 0; t < 2; t++) {
+        const int r = 2 * t + (mi & 1);
+        a_addr[t] = P_s + (uint32_t)((r * 6 + jj) * Wp + 16 * (mi >> 1));
+      }
+    }
+    // de-interleave work split: item i = (row, 16-pixel chunk), i = tid, tid + T, ...
+    const int nch = (d.W + 15) >> 4;
+    const int di_r0 = tid / nch, di_m0 = tid - di_r0 * nch;
+    const int di_dr = nthreads / nch, di_dm = nthreads - di_dr * nch;
+    // tmp4 word of this thread's two columns
+    uint8_t* dimg = dst + (size_t)img * C * out_h * out_w * elem;
+    int yy_next = yy0;
+    int slotA = 0, slotB = ng > 1 ? 1 : 0;  // ring slots of the step's two row groups
+
+    for (int s = s_first; s <= s_last; s++) {
+      const int nrows = min(8, d.H - 8 * s);
+      mbar_wait(&bars[0], tma_phase);
+      tma_phase ^= 1u;
+      // ---- de-interleave: 16 pixels (48 bytes) of one row -> three 16-byte planar pieces ------------
+      {
+        int r = di_r0, m = di_m0;
+        while (r < nrows) {
+          const uint4* sp = reinterpret_cast<const uint4*>(raw + (size_t)r * d.pitch + 48 * m);
+          const uint4 v0 = sp[0], v1 = sp[1], v2 = sp[2];
+          const uint32_t x[12] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};
+          uint32_t R[4], G[4], B[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const uint32_t x0 = x[3 * q], x1 = x[3 * q + 1], x2 = x[3 * q + 2];  // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+            R[q] = __byte_perm(__byte_perm(x0, x1, 0x0630), x2, 0x5210);
+            G[q] = __byte_perm(__byte_perm(x0, x1, 0x0741), x2, 0x6210);
+            B[q] = __byte_perm(__byte_perm(x0, x1, 0x0052), x2, 0x7410);
+          }
+          uint8_t* pl = P + (size_t)(((r & 3) * 6 + (r >> 2)) * Wp + 16 * m);
+          *reinterpret_cast<uint4*>(pl) = make_uint4(R[0], R[1], R[2], R[3]);
+          *reinterpret_cast<uint4*>(pl + 2 * Wp) = make_uint4(G[0], G[1], G[2], G[3]);
+          *reinterpret_cast<uint4*>(pl + 4 * Wp) = make_uint4(B[0], B[1], B[2], B[3]);
+          r += di_dr; m += di_dm;
+          if (m >= nch) { m -= nch; r++; }
+        }
+      }
+      __syncthreads();  // raw drained, P complete
+      if (tid == 0 && s < s_last) issue(s + 1);
+      // ---- horizontal pass: IMMA ----------------------------------------------------------------------
+#pragma unroll
+      for (int q = 0; q < kMmaTilesPerWarp; q++) {
+        const int nt = warp * kMmaTilesPerWarp + q;
+        if (nt < ntiles) {  // warp-uniform
+          uint32_t u[2][4];
+#pragma unroll
+          for (int t = 0; t < 2; t++) {
+            int acc[3][4];
+#pragma unroll
+            for (int ks = 0; ks < NK; ks++) {
+              uint32_t a[4];
+              ldsm_x4(a, a_addr[t] + (uint32_t)(s_nt[q] + 32 * ks));
+#pragma unroll
+              for (int p = 0; p < 3; p++) {
+                if (ks == 0) imma_16832_first(acc[p], a, bfr[q][ks][p][0], bfr[q][ks][p][1]);
+                else imma_16832(acc[p], a, bfr[q][ks][p][0], bfr[q][ks][p][1]);
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; k++)  // <= 255, see coeffs_never_clip
+              u[t][k] = ((uint32_t)acc[0][k] + ((uint32_t)acc[1][k] << 8) + ((uint32_t)acc[2][k] << 16) +
+                         (1u << (kPrecisionBits - 1))) >> kPrecisionBits;
+          }
+          // rows 0..3 = (t0.c0/c1, t0.c2/c3, t1.c0/c1, t1.c2/c3) for columns 2*tig / 2*tig + 1
+          const uint32_t w0 = __byte_perm(__byte_perm(u[0][0], u[0][2], 0x0040), __byte_perm(u[1][0], u[1][2], 0x0040), 0x5410);
+          const uint32_t w1 = __byte_perm(__byte_perm(u[0][1], u[0][3], 0x0040), __byte_perm(u[1][1], u[1][3], 0x0040), 0x5410);
+          const int col = nt * 8 + 2 * tig;
+          if (own) {
+            uint32_t* o = tmp4 + (size_t)(own_half ? slotB : slotA) * L;
+            if (nchw) {
+              if (col < out_w) o[own_ch * out_w + col] = w0;
+              if (col + 1 < out_w) o[own_ch * out_w + col + 1] = w1;
+            } else {
+              if (col < out_w) o[col * C + own_ch] = w0;
+              if (col + 1 < out_w) o[(col + 1) * C + own_ch] = w1;
+            }
+          }
+        }
+      }
+      __syncthreads();  // P free again, ring slots visible
+      // ---- vertical pass of the output rows whose last row group is now in the ring ------------------------
+      const int g_now = 2 * s + 1;
+      for (;;) {
+        int nready = 0;
+        for (int k = 0; k < vb_rows; k++) {
+          if (yy_next + k < yy1 && vg[2 * (yy_next + k) + 1] <= g_now) nready++; else break;
+        }
+        if (nready == 0) break;
+        if (vec4) {
+          if (vk < nready) {
+            const int yy = yy_next + vk;
+            const int gv0 = vg[2 * yy];
+            int slot0 = slotB - (g_now - gv0);
+            if (slot0 < 0) slot0 += ng;
+            const uint4* vc = reinterpret_cast<const uint4*>(pool + d.vc_off) + (size_t)yy * d.nwv;
+            for (int uu = vu0; uu < n_units; uu += nthreads) {
+              int ln = 0, x4 = uu;
+              if (nchw) { ln = uu / upl; x4 = uu - ln * upl; }
+              const int i0 = nchw ? ln * out_w + 4 * x4 : 4 * uu;
+              uint32_t a[4][3];
+#pragma unroll
+              for (int v = 0; v < 4; v++) { a[v][0] = 1u << (kPrecisionBits - 1); a[v][1] = 0; a[v][2] = 0; }
+              const uint32_t* tbase = tmp4 + i0;
+              auto tap = [&](int j, int slot) {
+                const uint4 kk = __ldg(vc + j);
+                const uint4 px = *reinterpret_cast<const uint4*>(tbase + slot * L);
+                a[0][0] = __dp4a(px.x, kk.x, a[0][0]); a[0][1] = __dp4a(px.x, kk.y, a[0][1]); a[0][2] = __dp4a(px.x, kk.z, a[0][2]);
+                a[1][0] = __dp4a(px.y, kk.x, a[1][0]); a[1][1] = __dp4a(px.y, kk.y, a[1][1]); a[1][2] = __dp4a(px.y, kk.z, a[1][2]);
+                a[2][0] = __dp4a(px.z, kk.x, a[2][0]); a[2][1] = __dp4a(px.z, kk.y, a[2][1]); a[2][2] = __dp4a(px.z, kk.z, a[2][2]);
+                a[3][0] = __dp4a(px.w, kk.x, a[3][0]); a[3][1] = __dp4a(px.w, kk.y, a[3][1]); a[3][2] = __dp4a(px.w, kk.z, a[3][2]);
+              };
+              auto taps = [&](auto NWVc) {
+                constexpr int NWV = decltype(NWVc)::value;
+#pragma unroll
+                for (int j = 0; j < NWV; j++) {
+                  int slot = slot0 + j;
+                  if (slot >= ng) slot -= ng;
+                  tap(j, slot);
+                }
+              };
+              switch (d.nwv) {
+                case 2: taps(std::integral_constant<int, 2>{}); break;
+                case 3: taps(std::integral_constant<int, 3>{}); break;
+                case 4: taps(std::integral_constant<int, 4>{}); break;
+                default: {
+                  int slot = slot0;
+                  for (int j = 0; j < d.nwv; j++) {
+                    tap(j, slot);
+                    if (++slot == ng) slot = 0;
+                  }
+                }
+              }
+              uint32_t u[4];
+#pragma unroll
+              for (int v = 0; v < 4; v++) u[v] = (a[v][0] + (a[v][1] << 8) + (a[v][2] << 16)) >> kPrecisionBits;
+              int c0, c1, c2, c3;
+              size_t e0;
+              if (nchw) {
+                c0 = c1 = c2 = c3 = ln * 256;
+                e0 = ((size_t)ln * out_h + yy) * out_w + 4 * x4;
+              } else {
+                const int m3 = uu % 3;  // (4 * uu) % 3
+                const int n1 = m3 == 2 ? 0 : m3 + 1, n2 = n1 == 2 ? 0 : n1 + 1;
+                c0 = m3 * 256; c1 = n1 * 256; c2 = n2 * 256; c3 = c0;
+                e0 = (size_t)yy * L + 4 * uu;
+              }
+              if (elem == 4) {
+                const uint32_t* l32 = reinterpret_cast<const uint32_t*>(lut);
+                st_global_v4(dimg + e0 * 4, __ldg(l32 + c0 + u[0]), __ldg(l32 + c1 + u[1]), __ldg(l32 + c2 + u[2]),
+                             __ldg(l32 + c3 + u[3]));
+              } else if (elem == 2) {
+                const uint16_t* l16 = reinterpret_cast<const uint16_t*>(lut);
+                const uint32_t lo = __ldg(l16 + c0 + u[0]) | ((uint32_t)__ldg(l16 + c1 + u[1]) << 16);
+                const uint32_t hi = __ldg(l16 + c2 + u[2]) | ((uint32_t)__ldg(l16 + c3 + u[3]) << 16);
+                st_global_v2(dimg + e0 * 2, lo, hi);
+              } else if (elem == 1) {
+                const uint32_t w = __ldg(lut + c0 + u[0]) | ((uint32_t)__ldg(lut + c1 + u[1]) << 8) |
+                                   ((uint32_t)__ldg(lut + c2 + u[2]) << 16) | ((uint32_t)__ldg(lut + c3 + u[3]) << 24);
+                *reinterpret_cast<uint32_t*>(dimg + e0) = w;
+              } else {
+                const uint2* l64 = reinterpret_cast<const uint2*>(lut);
+                const uint2 q0 = __ldg(l64 + c0 + u[0]), q1 = __ldg(l64 + c1 + u[1]);
+                const uint2 q2 = __ldg(l64 + c2 + u[2]), q3 = __ldg(l64 + c3 + u[3]);
+                st_global_v4(dimg + e0 * 8, q0.x, q0.y, q1.x, q1.y);
+                st_global_v4(dimg + e0 * 8 + 16, q2.x, q2.y, q3.x, q3.y);
+              }
+            }
+          }
+        } else {  // destination not 16-byte aligned / odd row length: one element at a time
+          nready = 1;
+          const int yy = yy_next;
+          const int gv0 = vg[2 * yy];
+          int slot0 = slotB - (g_now - gv0);
+          if (slot0 < 0) slot0 += ng;
+          const uint4* vc = reinterpret_cast<const uint4*>(pool + d.vc_off) + (size_t)yy * d.nwv;
+          for (int i = tid; i < L; i += nthreads) {
+            uint32_t a0 = 1u << (kPrecisionBits - 1), a1 = 0, a2 = 0;
+            int slot = slot0;
+            for (int j = 0; j < d.nwv; j++) {
+              const uint32_t px = tmp4[(size_t)slot * L + i];
+              const uint4 kk = __ldg(vc + j);
+              a0 = __dp4a(px, kk.x, a0); a1 = __dp4a(px, kk.y, a1); a2 = __dp4a(px, kk.z, a2);
+              if (++slot == ng) slot = 0;
+            }
+            const uint32_t u = (a0 + (a1 << 8) + (a2 << 16)) >> kPrecisionBits;
+            size_t e;
+            int ch;
+            if (nchw) { ch = i / out_w; e = ((size_t)ch * out_h + yy) * out_w + (i - ch * out_w); }
+            else { ch = i % C; e = (size_t)yy * L + i; }
+            const uint8_t* le = lut + ((size_t)ch * 256 + u) * elem;
+            if (elem == 4) reinterpret_cast<uint32_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint32_t*>(le));
+            else if (elem == 2) reinterpret_cast<uint16_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint16_t*>(le));
+            else if (elem == 1) dimg[e] = __ldg(le);
+            else reinterpret_cast<unsigned long long*>(dimg)[e] = __ldg(reinterpret_cast<const unsigned long long*>(le));
+          }
+        }
+        yy_next += nready;
+      }
+      // next step's groups go to the two slots after slotB
+      slotA = slotB + 1; if (slotA >= ng) slotA -= ng;
+      slotB = slotA + 1; if (slotB >= ng) slotB -= ng;
+    }
+  }  // work items of this CTA
+}
+
 // ---- host side ---------------------------------------------------------------------------------------
 // Packs Pillow's int32 coefficients of one axis into dp4a byte planes on the 4-sample word grid.
 // Returns the words per output (max over outputs); first[xx] = first word index.
@@ -588,6 +934,36 @@ static int nw_class(int nw) {
   return -1;
 }
 
+// Source-pixel windows of the IMMA variant: tile nt = output columns [8nt, 8nt + 8) reads the pixels
+// [start[nt], start[nt] + 32 * nk), start a multiple of 16 (ldmatrix rows are 16-byte pieces).
+struct MmaWindows {
+  int ntiles = 0, nk = 0, wp = 0;
+  std::vector<int32_t> start;
+};
+
+static MmaWindows mma_windows(const std::vector<int32_t>& bounds, int W, int out_w) {
+  MmaWindows m;
+  m.ntiles = (out_w + 7) / 8;
+  m.start.resize(m.ntiles);
+  int extent_max = 0, end_max = 0;
+  for (int nt = 0; nt < m.ntiles; nt++) {
+    const int c0 = nt * 8, c1 = std::min(nt * 8 + 7, out_w - 1);
+    int lo = bounds[2 * c0], hi = 0;
+    for (int cc = c0; cc <= c1; cc++) {
+      lo = std::min(lo, bounds[2 * cc]);
+      hi = std::max(hi, bounds[2 * cc] + bounds[2 * cc + 1]);
+    }
+    m.start[nt] = lo & ~15;
+    extent_max = std::max(extent_max, hi - m.start[nt]);
+  }
+  m.nk = (extent_max + 31) / 32;
+  for (int nt = 0; nt < m.ntiles; nt++) end_max = std::max(end_max, m.start[nt] + 32 * m.nk);
+  int wp = (int)round_up((uint64_t)std::max(end_max, W), 16);
+  while (wp % 128 != 16) wp += 16;  // six consecutive lines of one ldmatrix fall on distinct bank groups
+  m.wp = wp;
+  return m;
+}
+
 static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc& d, FusedGeom* g) {
   (void)elem;
   if (d.p1_axis != AXIS_H || d.p2_axis != AXIS_V) return false;
@@ -610,6 +986,27 @@ static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc&
   g->stage_bytes = (int)round_up((uint64_t)4 * d.pitch + 48, 128);
   g->threads = out_w > 256 ? 512 : 256;
   g->smem = 64 + (size_t)g->stage_bytes + (size_t)c * g->wq * 16 + (size_t)(nwv + 1) * out_w * c * 4 + 64;
+  g->mma_nk = 0;
+  // IMMA variant: RGB -> RGB, every row 16-byte aligned, windows of at most three 32-pixel k-steps
+  static const bool mma_on = !(getenv("TCB_FUSED_MMA") && atoi(getenv("TCB_FUSED_MMA")) == 0);
+  if (mma_on && c == 3 && d.cin == 3 && d.pitch % 16 == 0 && reinterpret_cast<uintptr_t>(d.src) % 16 == 0 &&
+      out_w <= 512) {
+    std::vector<int32_t> bh, kh;
+    compute_axis_coeffs(d.W, out_w, bh, kh);
+    MmaWindows mw = mma_windows(bh, d.W, out_w);
+    if (mw.nk >= 1 && mw.nk <= 3) {
+      const int stage = (int)round_up((uint64_t)8 * d.pitch + 64, 128);
+      const size_t smem = 128 + (size_t)stage + (size_t)kMmaLines * mw.wp + (size_t)(nwv + 1) * out_w * 3 * 4;
+      const int warps = (mw.ntiles + kMmaTilesPerWarp - 1) / kMmaTilesPerWarp;
+      if (smem <= kFusedMaxSmem) {
+        g->mma_nk = mw.nk; g->mma_wp = mw.wp;
+        g->nw_class = 100 + 2 * mw.nk + (warps > 14 ? 1 : 0);
+        g->stage_bytes = stage;
+        g->threads = warps * 32;
+        g->smem = smem;
+      }
+    }
+  }
   return g->smem <= kFusedMaxSmem;
 }
 
@@ -634,7 +1031,9 @@ struct FusedPlan {
 static FusedPlan* fused_of(const Plan& p) { return static_cast<FusedPlan*>(p.fused); }
 
 static const FusedGeom& cached_geometry(Plan& p, const ImgDesc& d) {
-  const std::array<int, 4> key = {d.W, d.H, d.cin, d.pitch};
+  // the IMMA variant also needs 16-byte aligned rows: the source alignment is part of the key
+  const int al16 = reinterpret_cast<uintptr_t>(d.src) % 16 == 0 ? 256 : 0;
+  const std::array<int, 4> key = {d.W, d.H, d.cin | al16, d.pitch};
   auto it = p.geom_cache.find(key);
   if (it == p.geom_cache.end()) {
     FusedGeom g;
@@ -662,6 +1061,13 @@ static int with_kernel(int cls, int c, bool big, F&& f) {
     return c == 3 ? f(k_preprocess_fused<NWv, 3, false>) : f(k_preprocess_fused<NWv, 1, false>);
   switch (cls) {
     TCB_K(2) TCB_K(3) TCB_K(4) TCB_K(5) TCB_K(6) TCB_K(8) TCB_K(10) TCB_K(12) TCB_K(16)
+    // IMMA variant: 100 + 2 * k-steps + (more than 14 warps)
+    case 102: return f(k_preprocess_fused_mma<1, 14>);
+    case 103: return f(k_preprocess_fused_mma<1, 32>);
+    case 104: return f(k_preprocess_fused_mma<2, 14>);
+    case 105: return f(k_preprocess_fused_mma<2, 32>);
+    case 106: return f(k_preprocess_fused_mma<3, 14>);
+    case 107: return f(k_preprocess_fused_mma<3, 32>);
     default: return set_error(TCB_ERR_INTERNAL, "bad coefficient class %d", cls);
   }
 #undef TCB_K
@@ -725,7 +1131,41 @@ int fused_prepare(Plan& p) {
     f.nw = g.nw_class; f.nwv = g.nwv; f.band_rows = 0; f.wq = g.wq;
     f.stage_bytes = g.stage_bytes;
     f.aligned4 = (reinterpret_cast<uintptr_t>(d.src) % 4 == 0) && (d.pitch % 4 == 0);
+    f.mma_nk = g.mma_nk; f.mma_wp = g.mma_wp; f.mma_b_off = 0; f.mma_s_off = 0;
     auto hk = std::make_pair(d.W, g.nw_class);
+    if (g.mma_nk > 0 && !htab.count(hk)) {
+      // B fragments of mma.m16n8k32 (col-major B: lane = 4 * column + k/4, two words = k 0..15 / 16..31
+      // quarter `lane & 3`), one set per (tile of 8 columns, k-step, coefficient byte plane)
+      std::vector<int32_t> b, k;
+      const int ks = compute_axis_coeffs(d.W, p.out_w, b, k);
+      const MmaWindows mw = mma_windows(b, d.W, p.out_w);
+      std::array<int32_t, 3> e;
+      align4(); e[0] = (int32_t)pool.size();
+      for (int nt = 0; nt < mw.ntiles; nt++)
+        for (int kstep = 0; kstep < mw.nk; kstep++)
+          for (int pl = 0; pl < 3; pl++)
+            for (int ln = 0; ln < 32; ln++)
+              for (int half = 0; half < 2; half++) {
+                const int col = nt * 8 + (ln >> 2);
+                uint32_t word = 0;
+                if (col < p.out_w) {
+                  const int xmin = b[2 * col], cnt = b[2 * col + 1];
+                  for (int bi = 0; bi < 4; bi++) {
+                    const int x = mw.start[nt] + 32 * kstep + 16 * half + 4 * (ln & 3) + bi;
+                    const int t = x - xmin;
+                    if (t >= 0 && t < cnt) {
+                      const uint32_t kv = (uint32_t)k[(size_t)col * ks + t];
+                      word |= ((kv >> (8 * pl)) & 0xffu) << (8 * bi);
+                    }
+                  }
+                }
+                pool.push_back((int32_t)word);
+              }
+      align4(); e[1] = (int32_t)pool.size(); pool.insert(pool.end(), mw.start.begin(), mw.start.end());
+      e[2] = 0;
+      htab[hk] = e;
+    }
+    if (g.mma_nk > 0) { f.mma_b_off = htab[hk][0]; f.mma_s_off = htab[hk][1]; }
     if (!htab.count(hk)) {
       std::vector<int32_t> b, k, packed, first;
       const int ks = compute_axis_coeffs(d.W, p.out_w, b, k);
@@ -829,7 +1269,8 @@ int fused_update_sources(const Plan& p, cudaStream_t s) {
       FusedDesc& f = fp->desc[i];
       f.src = p.h_desc[i].src;
       f.pitch = p.h_desc[i].pitch;
-      f.stage_bytes = (int)round_up((uint64_t)4 * f.pitch + 48, 128);  // follows the pitch (fused_accepts checked the fit)
+      // follows the pitch (fused_accepts checked the fit)
+      f.stage_bytes = f.mma_nk > 0 ? (int)round_up((uint64_t)8 * f.pitch + 64, 128) : (int)round_up((uint64_t)4 * f.pitch + 48, 128);
       f.aligned4 = (reinterpret_cast<uintptr_t>(f.src) % 4 == 0) && (f.pitch % 4 == 0);  // may change from run to run
     }
   TCB_CUDA(cudaMemcpyAsync(fp->d_desc, fp->desc.data(), sizeof(FusedDesc) * p.n, cudaMemcpyHostToDevice, s));
