@@ -771,6 +771,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--also", default="all", help="comma list of side benchmarks (%s), 'all' or 'none'" % ",".join(ALSO_ALL))
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline legs")
+    ap.add_argument("--no-e2e", action="store_true", help="kernel-only run (experiments; the e2e object is then null)")
     args = ap.parse_args()
     args.also = ALSO_ALL if args.also == "all" else [x for x in args.also.split(",") if x]
     rank = int(os.environ.get("RANK", "0"))
@@ -871,73 +872,79 @@ def main():
     parity = cx.sum_over_ranks(1.0 if parity_local else 0.0) == world
     del got
 
-    # ---- end to end: host buffers in, result read back, through the public API -------------------
-    h_batch = torch.empty((n, H, W, 3), dtype=torch.uint8, pin_memory=True)
-    h_batch.copy_(batch)
-    h_out = torch.empty(out_bytes, dtype=torch.uint8, pin_memory=True)
-    in_bytes = n * H * W * 3
+    e2e_value = e2e_ok = h2d_ceiling_gbs = pageable = None
+    e2e_steps, in_bytes = 0, n * H * W * 3
+    if args.no_e2e:
+        del batch
+        torch.cuda.empty_cache()
+    else:
+        # ---- end to end: host buffers in, result read back, through the public API -------------------
+        h_batch = torch.empty((n, H, W, 3), dtype=torch.uint8, pin_memory=True)
+        h_batch.copy_(batch)
+        h_out = torch.empty(out_bytes, dtype=torch.uint8, pin_memory=True)
+        in_bytes = n * H * W * 3
 
-    # (a) what the box gives: a bare pinned -> device copy of the same bytes on all ranks at once
-    stage = torch.empty(in_bytes, dtype=torch.uint8, device=cx.device)
-    cur = torch.cuda.current_stream(dev).cuda_stream
+        # (a) what the box gives: a bare pinned -> device copy of the same bytes on all ranks at once
+        stage = torch.empty(in_bytes, dtype=torch.uint8, device=cx.device)
+        cur = torch.cuda.current_stream(dev).cuda_stream
 
-    def bare_copy():
-        _lib.check(_lib.lib.TcbMemcpy(dev, stage.data_ptr(), h_batch.data_ptr(), in_bytes, cur, 0))
+        def bare_copy():
+            _lib.check(_lib.lib.TcbMemcpy(dev, stage.data_ptr(), h_batch.data_ptr(), in_bytes, cur, 0))
 
-    t_copy = cx.time_calls(bare_copy, steps=5, warmup=2)
-    h2d_ceiling_gbs = world * in_bytes / t_copy / 1e9
-    del stage
+        t_copy = cx.time_calls(bare_copy, steps=5, warmup=2)
+        h2d_ceiling_gbs = world * in_bytes / t_copy / 1e9
+        del stage
 
-    pipe = HostBatchPipeline(n, W, H, 3, CFG3["format"], CFG3["dtype"], CFG3["c"], CFG3["h"], CFG3["w"],
-                             CFG3["scaling"], device=dev, chunks=8)
+        pipe = HostBatchPipeline(n, W, H, 3, CFG3["format"], CFG3["dtype"], CFG3["c"], CFG3["h"], CFG3["w"],
+                                 CFG3["scaling"], device=dev, chunks=8)
 
-    def e2e_step():
-        pipe.run(h_batch.data_ptr(), region._base_addr, out_bytes, h_out.data_ptr())
+        def e2e_step():
+            pipe.run(h_batch.data_ptr(), region._base_addr, out_bytes, h_out.data_ptr())
 
-    e2e_steps = max(3, min(args.steps, 10))
-    for _ in range(3):
-        e2e_step()
-    torch.cuda.synchronize()
-    cx.barrier()
-    e0.record()
-    for _ in range(e2e_steps):
-        e2e_step()
-    e1.record()
-    torch.cuda.synchronize()
-    cx.barrier()
-    t_e2e = cx.max_over_ranks(e0.elapsed_time(e1) * 1e-3)
-    e2e_value = world * n * e2e_steps / t_e2e
-    # the bytes that came back over PCIe are the ones the device-resident run produced
-    ref_out = torch.empty(out_bytes, dtype=torch.uint8, pin_memory=True)
-    step()
-    _lib.check(_lib.lib.TcbRegionGet(region._c_handle, 0, ref_out.data_ptr(), out_bytes,
-                                     torch.cuda.current_stream(dev).cuda_stream))
-    e2e_ok = cx.sum_over_ranks(1.0 if torch.equal(ref_out, h_out) else 0.0) == world
-
-    # (c) the same pipeline from ordinary pageable memory (what the reference API hands over)
-    pageable = None
-    try:
-        src_np = np.empty((n, H, W, 3), dtype=np.uint8)
-        np.copyto(src_np, h_batch.numpy())
-        out_np = np.empty(out_bytes, dtype=np.uint8)
-        pipe.run_pageable(src_np, region._base_addr, out_bytes, out_np)
-        cx.barrier()
-        t0 = time.perf_counter()
-        reps = 3
-        for _ in range(reps):
-            pipe.run_pageable(src_np, region._base_addr, out_bytes, out_np)
+        e2e_steps = max(3, min(args.steps, 10))
+        for _ in range(3):
+            e2e_step()
         torch.cuda.synchronize()
-        t_pg = cx.max_over_ranks(time.perf_counter() - t0)
-        pg_ok = cx.sum_over_ranks(1.0 if np.array_equal(out_np, ref_out.numpy()) else 0.0) == world
-        pageable = {"value": world * n * reps / t_pg, "unit": "images/s", "matches_device_run": pg_ok,
-                    "path": "HostBatchPipeline.run_pageable: numpy array -> CPU copy into two pinned staging buffers -> "
-                            "H2D | kernel | D2H -> numpy array (wall clock, %d passes)" % reps}
-        del src_np, out_np
-    except Exception as ex:
-        pageable = {"error": repr(ex)[:300]}
-    pipe.close()
-    del h_batch, pipe, ref_out, h_out, batch
-    torch.cuda.empty_cache()
+        cx.barrier()
+        e0.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        e1.record()
+        torch.cuda.synchronize()
+        cx.barrier()
+        t_e2e = cx.max_over_ranks(e0.elapsed_time(e1) * 1e-3)
+        e2e_value = world * n * e2e_steps / t_e2e
+        # the bytes that came back over PCIe are the ones the device-resident run produced
+        ref_out = torch.empty(out_bytes, dtype=torch.uint8, pin_memory=True)
+        step()
+        _lib.check(_lib.lib.TcbRegionGet(region._c_handle, 0, ref_out.data_ptr(), out_bytes,
+                                         torch.cuda.current_stream(dev).cuda_stream))
+        e2e_ok = cx.sum_over_ranks(1.0 if torch.equal(ref_out, h_out) else 0.0) == world
+
+        # (c) the same pipeline from ordinary pageable memory (what the reference API hands over)
+        pageable = None
+        try:
+            src_np = np.empty((n, H, W, 3), dtype=np.uint8)
+            np.copyto(src_np, h_batch.numpy())
+            out_np = np.empty(out_bytes, dtype=np.uint8)
+            pipe.run_pageable(src_np, region._base_addr, out_bytes, out_np)
+            cx.barrier()
+            t0 = time.perf_counter()
+            reps = 3
+            for _ in range(reps):
+                pipe.run_pageable(src_np, region._base_addr, out_bytes, out_np)
+            torch.cuda.synchronize()
+            t_pg = cx.max_over_ranks(time.perf_counter() - t0)
+            pg_ok = cx.sum_over_ranks(1.0 if np.array_equal(out_np, ref_out.numpy()) else 0.0) == world
+            pageable = {"value": world * n * reps / t_pg, "unit": "images/s", "matches_device_run": pg_ok,
+                        "path": "HostBatchPipeline.run_pageable: numpy array -> CPU copy into two pinned staging buffers -> "
+                                "H2D | kernel | D2H -> numpy array (wall clock, %d passes)" % reps}
+            del src_np, out_np
+        except Exception as ex:
+            pageable = {"error": repr(ex)[:300]}
+        pipe.close()
+        del h_batch, pipe, ref_out, h_out, batch
+        torch.cuda.empty_cache()
 
     # ---- the other BASELINE configs ---------------------------------------------------------------
     also = {}
@@ -988,7 +995,7 @@ def main():
             "roofline": roofline(algo, kern_s, peak, "k_preprocess_fused_cfg3", peak_source=peak_src,
                                  kernel="all kernels of one step (%d launch(es)/step)" % (launches // max(args.steps, 1))),
             "cpu_baseline": cpu,
-            "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": world * in_bytes,
+            "e2e": None if args.no_e2e else {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": world * in_bytes,
                     "d2h_bytes_per_step": world * out_bytes, "steps": e2e_steps,
                     "path": "HostBatchPipeline.run: pinned host batch -> 8 chunks x (TcbMemcpy H2D | TcbPreprocessPlanRun "
                             "into the region | TcbMemcpy D2H of the result) on two streams",

@@ -121,15 +121,27 @@ typedef struct TcbImage {
  *             image_client.py:171-182) on arange(256), which makes the dtype conversion and
  *             scaling bit-exact for every dtype, including numpy's fp16 double rounding.
  *  elem_size: 1, 2, 4 or 8
- *  path     : 0 = auto (fused kernel where it applies, two-pass kernels otherwise), 1 = force the
- *             two-pass kernels, 2 = require the fused kernel (TCB_ERR_UNSUPPORTED if any image's
- *             geometry does not fit it).
+ *  path     : 0 = auto (a fused kernel where one applies, two-pass kernels otherwise), 1 = force the
+ *             two-pass kernels, 2 = require a fused kernel (TCB_ERR_UNSUPPORTED if any image's
+ *             geometry does not fit one), 3 = like 2 but never the IMMA variant. There are two fused
+ *             kernels: an IMMA (int8 tensor-core) one for RGB sources whose rows are 16-byte aligned
+ *             (base pointer and pitch multiples of 16) and a dp4a one for everything else.
  * Image i is written at dst_dev + i * c*out_h*out_w*elem_size. */
 int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images, int c, int out_h,
                             int out_w, int layout, const void* lut, int elem_size, int path,
                             void** plan);
 /* Source pointers/pitches may change between runs (same sizes); pass NULL to keep the ones
- * given at creation (src_dev may be 0 at creation if every run supplies pointers).
+ * given at creation (src_dev may be 0 at creation if every run supplies pointers). The launch
+ * (which kernel, how much shared memory) is fixed at creation: a run whose new pointers or pitches
+ * no longer fit it - rows that lose the alignment the chosen kernel needs, a pitch far larger than
+ * the plan's - returns TCB_ERR_UNSUPPORTED and changes nothing; create a new plan then. A run that
+ * fails validation leaves the plan as it was.
+ * A plan is NOT re-entrant: it owns one set of device descriptors, rewritten on `stream` when the
+ * pointers change, so run one plan from one thread / one stream at a time (different plans are
+ * independent; there is no process-global state). The fused kernels fetch source rows with 16-byte
+ * granular bulk copies: the dp4a kernel may read up to 15 bytes before the first and after the last
+ * byte of an image whose rows are not 16-byte aligned (never outside the 16-byte blocks the image
+ * touches).
  * dst_capacity is the number of bytes available at dst_dev. */
 int TcbPreprocessPlanRun(void* plan, const TcbImage* images_or_null, void* dst_dev,
                          uint64_t dst_capacity, void* stream);

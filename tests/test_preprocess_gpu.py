@@ -354,7 +354,8 @@ def test_host_batch_pipeline_matches_oracle(chunks):
         cudashm.destroy_shared_memory_region(region)
 
 
-def test_plan_run_with_changed_pitch_and_failed_run_keeps_plan_consistent():
+@pytest.mark.parametrize("path", [2, 3], ids=["fused-auto", "fused-dp4a"])
+def test_plan_run_with_changed_pitch_and_failed_run_keeps_plan_consistent(path):
     """(1) a run may raise an image's pitch - the staging size must follow and the
     result stay exact; (2) a pitch the launch cannot hold is refused; (3) a run that fails
     validation half-way must not leave stale pointers behind."""
@@ -365,7 +366,7 @@ def test_plan_run_with_changed_pitch_and_failed_run_keeps_plan_consistent():
     from triton_client_b200 import _lib
 
     rng = np.random.default_rng(31)
-    shapes = [(480, 640), (300, 600)]  # (H, W): same coefficient class (one launch), different staging sizes
+    shapes = [(480, 640), (300, 592)]  # (H, W): rows of 16-byte multiples, same coefficient class (one launch), different staging sizes
     srcs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in shapes]
     lut = pb.scaling_lut("FP32", 3, "INCEPTION")
     lut_c = np.ascontiguousarray(lut)
@@ -382,11 +383,11 @@ def test_plan_run_with_changed_pitch_and_failed_run_keeps_plan_consistent():
             arr[i] = _lib.TcbImage(b.data_ptr(), shapes[i][1], shapes[i][0], p, 3)
         return arr
 
-    p0 = [640 * 3, 600 * 3]
+    p0 = [640 * 3, 592 * 3]
     bufs0 = [padded(a, p) for a, p in zip(srcs, p0)]
     plan = ctypes.c_void_p()
     _lib.check(_lib.lib.TcbPreprocessPlanCreate(0, images(bufs0, p0), 2, 3, 224, 224, _lib.LAYOUT_NCHW,
-                                                lut_c.ctypes.data, 4, 2, ctypes.byref(plan)))
+                                                lut_c.ctypes.data, 4, path, ctypes.byref(plan)))
     out = torch.zeros((2, 3, 224, 224), dtype=torch.float32, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
     want = [oracle_preprocess(a, 3, 224, 224, 2, "FP32", "INCEPTION") for a in srcs]
@@ -401,17 +402,24 @@ def test_plan_run_with_changed_pitch_and_failed_run_keeps_plan_consistent():
     for i in range(2):
         assert np.array_equal(out[i].cpu().numpy(), want[i])
     # (1) the SMALLER image's pitch grows (still below the larger image's): accepted and exact
-    p1 = [640 * 3, 600 * 3 + 100]
+    p1 = [640 * 3, 592 * 3 + 112]  # still a multiple of 16: both fused kernels take it
     bufs1 = [bufs0[0], padded(srcs[1], p1[1])]
     assert run(images(bufs1, p1)) == 0
     for i in range(2):
         assert np.array_equal(out[i].cpu().numpy(), want[i])
     # odd pitch: rows lose their 4-byte alignment, still exact
-    p2 = [640 * 3 + 1, 600 * 3 + 3]
+    p2 = [640 * 3 + 1, 592 * 3 + 3]
     bufs2 = [padded(a, p) for a, p in zip(srcs, p2)]
-    assert run(images(bufs2, p2)) == 0
-    for i in range(2):
-        assert np.array_equal(out[i].cpu().numpy(), want[i])
+    rc = run(images(bufs2, p2))
+    if path == 3:  # the dp4a kernel reads rows of any alignment
+        assert rc == 0
+    else:          # the IMMA kernel (chosen at creation for these 16-byte aligned rows) cannot: refused, nothing changed
+        assert rc in (0, _lib.TCB_ERR_UNSUPPORTED)
+    if rc == 0:
+        for i in range(2):
+            assert np.array_equal(out[i].cpu().numpy(), want[i])
+    else:
+        bufs2 = bufs1
     # (2) a pitch far beyond what the launch's shared memory was sized for is refused
     p3 = [640 * 3 + 1, 65536]
     bufs3 = [bufs2[0], padded(srcs[1], p3[1])]
@@ -422,7 +430,7 @@ def test_plan_run_with_changed_pitch_and_failed_run_keeps_plan_consistent():
         assert np.array_equal(out[i].cpu().numpy(), want[i])
     # geometry mismatch on image 1 after a changed pointer on image 0: nothing of it sticks either
     bad = images([bufs0[0], bufs0[1]], p0)
-    bad[1].width = 601
+    bad[1].width = 593
     assert run(bad) == _lib.TCB_ERR_INVALID_ARG
     del bufs0  # image 0's "new" pointer from the failed call dies here; the plan must not use it
     torch.cuda.empty_cache()

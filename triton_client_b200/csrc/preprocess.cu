@@ -302,7 +302,7 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
                             void** plan) {
   TCB_CHECK_ARG(plan != nullptr, "TcbPreprocessPlanCreate: plan out-pointer is NULL");
   *plan = nullptr;
-  TCB_CHECK_ARG(path >= 0 && path <= 2, "TcbPreprocessPlanCreate: path must be 0, 1 or 2");
+  TCB_CHECK_ARG(path >= 0 && path <= 3, "TcbPreprocessPlanCreate: path must be 0, 1, 2 or 3");
   TCB_CHECK_ARG(images != nullptr && n_images > 0, "TcbPreprocessPlanCreate: no images");
   TCB_CHECK_ARG(c == 1 || c == 3, "TcbPreprocessPlanCreate: c must be 1 or 3 (got %d)", c);
   TCB_CHECK_ARG(out_h > 0 && out_w > 0 && out_h <= 16384 && out_w <= 16384,
@@ -321,6 +321,7 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
   if (!p) return set_error(TCB_ERR_NOMEM, "out of host memory");
   p->device = device_id; p->n = n_images; p->c = c; p->out_h = out_h; p->out_w = out_w;
   p->layout = layout; p->elem = elem_size;
+  p->no_mma = path == 3;
 
   // coefficient tables, one per distinct (in, out) pair
   std::vector<int32_t> pool;
@@ -358,7 +359,7 @@ int TcbPreprocessPlanCreate(int device_id, const TcbImage* images, int n_images,
     if (d.p1_axis == AXIS_V || d.p2_axis == AXIS_V) d.tv = get_table(d.H, out_h);
     int band = 0; size_t smem = 0;
     const bool can_fuse = path != 1 && fused_supported(*p, d, &band, &smem);
-    if (path == 2 && !can_fuse) {
+    if (path >= 2 && !can_fuse) {
       const int fw = d.W, fh = d.H, fc = d.cin, fp = d.pitch;
       delete p;
       return set_error(TCB_ERR_UNSUPPORTED,

@@ -58,6 +58,7 @@ struct Plan {
   int32_t* d_fused_work = nullptr;  // pairs (image, first output row)
   int n_fused_ctas = 0, n_fused_images = 0;
   size_t fused_smem = 0;
+  bool no_mma = false;      // path 3: fused dp4a kernel only
   bool desc_dirty = false;  // host descriptors changed, device copies not yet re-uploaded
   // fused-kernel geometry per distinct (W, H, channels, pitch): a batch of thousands of images has a
   // handful of distinct sizes, and the coefficient set-up behind the answer is not free

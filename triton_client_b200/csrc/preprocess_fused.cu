@@ -91,6 +91,7 @@ struct FusedDesc {
   int32_t mma_wp;     // bytes per planar line in shared memory (multiple of 16, == 16 mod 128)
   int32_t mma_b_off;  // pool: B fragments [n-tile][k-step][plane][lane][2]
   int32_t mma_s_off;  // pool: first source pixel of every n-tile's window [n-tiles] (multiple of 16)
+  int32_t vq_off;     // pool: output rows complete after 8-row step s (last group <= 2s + 1) [ceil(H / 8)]
 };
 
 __device__ __forceinline__ uint32_t fetch_conv(const uint8_t* row, int cin, int C, int x, int ch) {
@@ -508,17 +509,20 @@ __device__ __forceinline__ void imma_16832(int (&c)[4], const uint32_t (&a)[4], 
       : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
-__device__ __forceinline__ void imma_16832_first(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+__device__ __forceinline__ void imma_16832_first(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1, int init) {
   asm volatile(
       "mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
       : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(0));
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(init));
 }
 
-constexpr int kMmaTilesPerWarp = 2;
 constexpr int kMmaLines = 24;  // 4 rows x 3 channels x 2 halves
 
-template <int NK, int WMAX>
+// TPW: 8-column tiles per warp. TPW = 2: up to 14 warps, two CTAs per SM (72 registers), the 36
+// fragment registers leave no room to interleave the accumulation chains. TPW = 1: up to 28 warps,
+// one CTA per SM (72 registers again), 18 fragment registers, both 16-line tiles of a column tile in
+// flight at once and ~115 KB of L1 left for tables.
+template <int NK, int TPW, int WMAX>
 __global__ void __launch_bounds__(WMAX * 32, WMAX <= 16 ? 2 : 1)
 k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restrict__ items,
                        const int32_t* __restrict__ cta_first, const int32_t* __restrict__ pool,
@@ -526,16 +530,21 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
                        int layout, int elem, int dst_aligned16) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int C = 3;
+  constexpr int kMmaTilesPerWarp = TPW;
   const int tid = threadIdx.x, nthreads = blockDim.x;
   const int lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, tig = lane & 3;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
   if (tid == 0) {
     mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  uint32_t tma_phase = 0;
+  // raw stages: two when the CTA has an SM to itself (the TMA of step s + 2 starts as soon as step s has
+  // been de-interleaved and has a whole step to land), one when two CTAs share the shared memory
+  constexpr int NST = TPW == 1 ? 2 : 1;
+  uint32_t tma_phase = 0;  // bit i: parity of the next completion of bars[i]; runs on across work items
   const bool nchw = layout == TCB_LAYOUT_NCHW;
   const int L = out_w * C;
   const int ntiles = (out_w + 7) >> 3;
@@ -544,12 +553,44 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
   const int upl = nchw ? out_w / 4 : L / 4;       // units (4 consecutive output elements) per line
   const int n_units = vec4 ? (nchw ? C * upl : upl) : 0;
   const int vb_rows = n_units > 0 ? max(1, nthreads / n_units) : 1;  // output rows handled side by side
-  const int vk = n_units > 0 ? tid / n_units : 0;
-  const int vu0 = n_units > 0 ? tid - vk * n_units : 0;
+  const int vk = n_units > 0 ? tid / n_units : 0;  // which of the side-by-side rows this thread serves (>= vb_rows: none)
+  int v_i0 = 0, v_e0 = 0, v_lut = 0;              // first tmp4 word, element offset at yy = 0, packed table rows
+  if (n_units > 0) {
+    const int vu0 = tid - vk * n_units;
+    if (nchw) {
+      const int ln = vu0 / upl, x4 = vu0 - ln * upl;
+      v_i0 = ln * out_w + 4 * x4;
+      v_e0 = v_i0 + ln * (out_h - 1) * out_w;
+      v_lut = (ln * 256) * (1 + 1024 + 1024 * 1024);
+    } else {
+      v_i0 = v_e0 = 4 * vu0;
+      const int m3 = vu0 % 3;  // (4 * vu0) % 3
+      const int n1 = m3 == 2 ? 0 : m3 + 1, n2 = n1 == 2 ? 0 : n1 + 1;
+      v_lut = (m3 * 256) | ((n1 * 256) << 10) | ((n2 * 256) << 20);
+    }
+  }
+  const int v_erow = nchw ? out_w : L;
+  // value table and (per item) the row -> (first group, last group) table live in shared memory: with two
+  // CTAs of ~110 KB per SM the L1 cache that would otherwise hold them is a few KB
+  uint8_t* lut_s = smem + 128;
+  int32_t* vg_s = reinterpret_cast<int32_t*>(lut_s + 768 * elem);
+  const int vg_bytes = (out_h * 8 + 127) & ~127;
+  for (int i = tid; i < 768 * elem / 4; i += nthreads)
+    reinterpret_cast<uint32_t*>(lut_s)[i] = __ldg(reinterpret_cast<const uint32_t*>(lut) + i);
   // ---- horizontal-pass constants --------------------------------------------------------------------
   // accumulator ownership: lines g, g+8 of both tiles = rows 0..3 of pair g = (channel g>>1, half g&1)
   const int own_ch = g >> 1, own_half = g & 1;
-  const bool own = g < 6;
+  const int st_cs = nchw ? 1 : C;  // tmp4 words between neighbouring columns
+  int st_base = 0, st_mask = 0;    // first word of this thread's columns (tile q = 0), which of its 4 stores exist
+  {
+    const int col0 = warp * kMmaTilesPerWarp * 8 + 2 * tig;
+    st_base = nchw ? own_ch * out_w + col0 : col0 * C + own_ch;
+    if (g < 6)
+      for (int q = 0; q < kMmaTilesPerWarp; q++) {
+        if (col0 + 8 * q < out_w) st_mask |= 1 << (2 * q);
+        if (col0 + 8 * q + 1 < out_w) st_mask |= 2 << (2 * q);
+      }
+  }
 
   for (int item = cta_first[blockIdx.x]; item < cta_first[blockIdx.x + 1]; item++) {
     const int4 wi = items[item];
@@ -558,26 +599,28 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
     const int ng = d.nwv + 1;
     const int Wp = d.mma_wp;
     // shared memory: barrier | raw stage (8 rows) | P lines | tmp4 ring
-    uint8_t* raw = smem + 128;
-    uint8_t* P = raw + d.stage_bytes;
+    uint8_t* raw = reinterpret_cast<uint8_t*>(vg_s) + vg_bytes;
+    uint8_t* P = raw + NST * d.stage_bytes;
     uint32_t* tmp4 = reinterpret_cast<uint32_t*>(P + (size_t)kMmaLines * Wp);
     const uint32_t P_s = smem_u32(P);
 
     const int32_t* vb = pool + d.vb_off;
-    const int32_t* vg = pool + d.vg_off;
     const int ys = vb[2 * yy0], ye = vb[2 * (yy1 - 1)] + vb[2 * (yy1 - 1) + 1];  // source rows [ys, ye)
     const int s_first = ys >> 3, s_last = (ye - 1) >> 3;
 
-    auto issue = [&](int s) {  // thread 0: rows [8s, min(8s + 8, H)) -> raw stage
+    auto issue = [&](int s) {  // thread 0: rows [8s, min(8s + 8, H)) -> raw stage (s - s_first) % NST
       const int r0 = 8 * s, r1 = min(r0 + 8, d.H);
+      const int st = (s - s_first) % NST;
       const uint8_t* a0 = d.src + (size_t)r0 * d.pitch;
       const uint32_t bytes = (uint32_t)((r1 - r0 - 1) * d.pitch + ((d.W * 3 + 15) & ~15));
-      mbar_expect_tx(&bars[0], bytes);
-      tma_load_1d(raw, a0, bytes, &bars[0]);
+      mbar_expect_tx(&bars[st], bytes);
+      tma_load_1d(raw + (size_t)st * d.stage_bytes, a0, bytes, &bars[st]);
     };
     // different images = different shared-memory layouts: see k_preprocess_fused
     if (item != cta_first[blockIdx.x]) __syncthreads();
-    if (tid == 0) issue(s_first);
+    if (tid == 0)
+      for (int i = 0; i < NST && s_first + i <= s_last; i++) issue(s_first + i);
+    for (int i = tid; i < 2 * out_h; i += nthreads) vg_s[i] = pool[d.vg_off + i];  // visible after the step's first barrier
 
     // ---- per-item constants ---------------------------------------------------------------------
     // B fragments of this warp's two tiles
@@ -623,15 +666,18 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
     int yy_next = yy0;
     int slotA = 0, slotB = ng > 1 ? 1 : 0;  // ring slots of the step's two row groups
 
+    int rows_done = pool[d.vq_off + s_first], rows_done_next = pool[d.vq_off + min(s_first + 1, s_last)];
     for (int s = s_first; s <= s_last; s++) {
       const int nrows = min(8, d.H - 8 * s);
-      mbar_wait(&bars[0], tma_phase);
-      tma_phase ^= 1u;
+      const int st = (s - s_first) % NST;
+      const uint8_t* rawst = raw + (size_t)st * d.stage_bytes;
+      mbar_wait(&bars[st], (tma_phase >> st) & 1u);
+      tma_phase ^= 1u << st;
       // ---- de-interleave: 16 pixels (48 bytes) of one row -> three 16-byte planar pieces ------------
       {
         int r = di_r0, m = di_m0;
         while (r < nrows) {
-          const uint4* sp = reinterpret_cast<const uint4*>(raw + (size_t)r * d.pitch + 48 * m);
+          const uint4* sp = reinterpret_cast<const uint4*>(rawst + (size_t)r * d.pitch + 48 * m);
           const uint4 v0 = sp[0], v1 = sp[1], v2 = sp[2];
           const uint32_t x[12] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};
           uint32_t R[4], G[4], B[4];
@@ -651,141 +697,121 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
         }
       }
       __syncthreads();  // raw drained, P complete
-      if (tid == 0 && s < s_last) issue(s + 1);
+      if (tid == 0 && s + NST <= s_last) issue(s + NST);  // into the stage that has just been drained
       // ---- horizontal pass: IMMA ----------------------------------------------------------------------
+      // (tiles beyond the last one compute on all-zero fragments and store nothing: no branch per tile)
+      uint32_t* st_ptr = tmp4 + (own_half ? slotB : slotA) * L + st_base;
 #pragma unroll
       for (int q = 0; q < kMmaTilesPerWarp; q++) {
-        const int nt = warp * kMmaTilesPerWarp + q;
-        if (nt < ntiles) {  // warp-uniform
-          uint32_t u[2][4];
+        uint32_t w0 = 0, w1 = 0;
 #pragma unroll
-          for (int t = 0; t < 2; t++) {
-            int acc[3][4];
+        for (int t = 0; t < 2; t++) {
+          int acc[3][4];
 #pragma unroll
-            for (int ks = 0; ks < NK; ks++) {
-              uint32_t a[4];
-              ldsm_x4(a, a_addr[t] + (uint32_t)(s_nt[q] + 32 * ks));
+          for (int ks = 0; ks < NK; ks++) {
+            uint32_t a[4];
+            ldsm_x4(a, a_addr[t] + (uint32_t)(s_nt[q] + 32 * ks));
 #pragma unroll
-              for (int p = 0; p < 3; p++) {
-                if (ks == 0) imma_16832_first(acc[p], a, bfr[q][ks][p][0], bfr[q][ks][p][1]);
-                else imma_16832(acc[p], a, bfr[q][ks][p][0], bfr[q][ks][p][1]);
-              }
-            }
-#pragma unroll
-            for (int k = 0; k < 4; k++)  // <= 255, see coeffs_never_clip
-              u[t][k] = ((uint32_t)acc[0][k] + ((uint32_t)acc[1][k] << 8) + ((uint32_t)acc[2][k] << 16) +
-                         (1u << (kPrecisionBits - 1))) >> kPrecisionBits;
-          }
-          // rows 0..3 = (t0.c0/c1, t0.c2/c3, t1.c0/c1, t1.c2/c3) for columns 2*tig / 2*tig + 1
-          const uint32_t w0 = __byte_perm(__byte_perm(u[0][0], u[0][2], 0x0040), __byte_perm(u[1][0], u[1][2], 0x0040), 0x5410);
-          const uint32_t w1 = __byte_perm(__byte_perm(u[0][1], u[0][3], 0x0040), __byte_perm(u[1][1], u[1][3], 0x0040), 0x5410);
-          const int col = nt * 8 + 2 * tig;
-          if (own) {
-            uint32_t* o = tmp4 + (size_t)(own_half ? slotB : slotA) * L;
-            if (nchw) {
-              if (col < out_w) o[own_ch * out_w + col] = w0;
-              if (col + 1 < out_w) o[own_ch * out_w + col + 1] = w1;
-            } else {
-              if (col < out_w) o[col * C + own_ch] = w0;
-              if (col + 1 < out_w) o[(col + 1) * C + own_ch] = w1;
+            for (int p = 0; p < 3; p++) {
+              // the fragments hold 4 * k, plane 0 starts from 4 * 2^21: the sum of the three planes then
+              // carries the rounded result (sum >> 22) in its top byte, where PRMT picks it up
+              if (ks == 0) imma_16832_first(acc[p], a, bfr[q][ks][p][0], bfr[q][ks][p][1], p == 0 ? (4 << (kPrecisionBits - 1)) : 0);
+              else imma_16832(acc[p], a, bfr[q][ks][p][0], bfr[q][ks][p][1]);
             }
           }
+          uint32_t u[4];
+#pragma unroll
+          for (int k = 0; k < 4; k++)  // top byte <= 255, see coeffs_never_clip
+            u[k] = (uint32_t)acc[0][k] + ((uint32_t)acc[1][k] << 8) + ((uint32_t)acc[2][k] << 16);
+          // rows 2t, 2t+1 (c0/c1 and c2/c3) of columns 2*tig / 2*tig + 1 -> byte lanes 2t, 2t+1
+          const uint32_t h0 = __byte_perm(u[0], u[2], 0x0073), h1 = __byte_perm(u[1], u[3], 0x0073);
+          w0 = t == 0 ? h0 : __byte_perm(w0, h0, 0x5410);
+          w1 = t == 0 ? h1 : __byte_perm(w1, h1, 0x5410);
         }
+        // this thread's two columns of pair g: index and guards fixed per thread
+        uint32_t* o = st_ptr + q * 8 * st_cs;
+        if (st_mask & (1 << (2 * q))) o[0] = w0;
+        if (st_mask & (2 << (2 * q))) o[st_cs] = w1;
       }
       __syncthreads();  // P free again, ring slots visible
       // ---- vertical pass of the output rows whose last row group is now in the ring ------------------------
+      // Every thread owns at most one unit (4 consecutive output elements) of one of the vb_rows rows
+      // handled side by side; everything that depends only on the thread was computed before the item
+      // loop (a first version recomputed unit -> line/column/table rows here and spent 40 % of the
+      // kernel's instructions in this block).
       const int g_now = 2 * s + 1;
-      for (;;) {
-        int nready = 0;
-        for (int k = 0; k < vb_rows; k++) {
-          if (yy_next + k < yy1 && vg[2 * (yy_next + k) + 1] <= g_now) nready++; else break;
-        }
-        if (nready == 0) break;
+      const int yend = min(rows_done, yy1);  // rows [yy_next, yend) have all their row groups in the ring
+      rows_done = rows_done_next;
+      if (s < s_last) rows_done_next = __ldg(pool + d.vq_off + min(s + 2, s_last));  // consumed two steps from now
+      while (yy_next < yend) {
+        int nready = min(vb_rows, yend - yy_next);
         if (vec4) {
           if (vk < nready) {
             const int yy = yy_next + vk;
-            const int gv0 = vg[2 * yy];
-            int slot0 = slotB - (g_now - gv0);
+            const int c0 = v_lut & 1023, c1 = (v_lut >> 10) & 1023, c2 = v_lut >> 20;  // table rows (the fourth equals the first)
+            int slot0 = slotB - (g_now - vg_s[2 * yy]);
             if (slot0 < 0) slot0 += ng;
             const uint4* vc = reinterpret_cast<const uint4*>(pool + d.vc_off) + (size_t)yy * d.nwv;
-            for (int uu = vu0; uu < n_units; uu += nthreads) {
-              int ln = 0, x4 = uu;
-              if (nchw) { ln = uu / upl; x4 = uu - ln * upl; }
-              const int i0 = nchw ? ln * out_w + 4 * x4 : 4 * uu;
-              uint32_t a[4][3];
+            uint32_t a[4][3];
 #pragma unroll
-              for (int v = 0; v < 4; v++) { a[v][0] = 1u << (kPrecisionBits - 1); a[v][1] = 0; a[v][2] = 0; }
-              const uint32_t* tbase = tmp4 + i0;
-              auto tap = [&](int j, int slot) {
-                const uint4 kk = __ldg(vc + j);
-                const uint4 px = *reinterpret_cast<const uint4*>(tbase + slot * L);
-                a[0][0] = __dp4a(px.x, kk.x, a[0][0]); a[0][1] = __dp4a(px.x, kk.y, a[0][1]); a[0][2] = __dp4a(px.x, kk.z, a[0][2]);
-                a[1][0] = __dp4a(px.y, kk.x, a[1][0]); a[1][1] = __dp4a(px.y, kk.y, a[1][1]); a[1][2] = __dp4a(px.y, kk.z, a[1][2]);
-                a[2][0] = __dp4a(px.z, kk.x, a[2][0]); a[2][1] = __dp4a(px.z, kk.y, a[2][1]); a[2][2] = __dp4a(px.z, kk.z, a[2][2]);
-                a[3][0] = __dp4a(px.w, kk.x, a[3][0]); a[3][1] = __dp4a(px.w, kk.y, a[3][1]); a[3][2] = __dp4a(px.w, kk.z, a[3][2]);
-              };
-              auto taps = [&](auto NWVc) {
-                constexpr int NWV = decltype(NWVc)::value;
+            for (int v = 0; v < 4; v++) { a[v][0] = 1u << (kPrecisionBits - 1); a[v][1] = 0; a[v][2] = 0; }
+            const uint32_t* tbase = tmp4 + v_i0;
+            auto tap = [&](int j, int slot) {
+              const uint4 kk = __ldg(vc + j);
+              const uint4 px = *reinterpret_cast<const uint4*>(tbase + slot * L);
+              a[0][0] = __dp4a(px.x, kk.x, a[0][0]); a[0][1] = __dp4a(px.x, kk.y, a[0][1]); a[0][2] = __dp4a(px.x, kk.z, a[0][2]);
+              a[1][0] = __dp4a(px.y, kk.x, a[1][0]); a[1][1] = __dp4a(px.y, kk.y, a[1][1]); a[1][2] = __dp4a(px.y, kk.z, a[1][2]);
+              a[2][0] = __dp4a(px.z, kk.x, a[2][0]); a[2][1] = __dp4a(px.z, kk.y, a[2][1]); a[2][2] = __dp4a(px.z, kk.z, a[2][2]);
+              a[3][0] = __dp4a(px.w, kk.x, a[3][0]); a[3][1] = __dp4a(px.w, kk.y, a[3][1]); a[3][2] = __dp4a(px.w, kk.z, a[3][2]);
+            };
+            auto taps = [&](auto NWVc) {
+              constexpr int NWV = decltype(NWVc)::value;
 #pragma unroll
-                for (int j = 0; j < NWV; j++) {
-                  int slot = slot0 + j;
-                  if (slot >= ng) slot -= ng;
+              for (int j = 0; j < NWV; j++) {
+                int slot = slot0 + j;
+                if (slot >= ng) slot -= ng;
+                tap(j, slot);
+              }
+            };
+            switch (d.nwv) {
+              case 2: taps(std::integral_constant<int, 2>{}); break;
+              case 3: taps(std::integral_constant<int, 3>{}); break;
+              case 4: taps(std::integral_constant<int, 4>{}); break;
+              default: {
+                int slot = slot0;
+                for (int j = 0; j < d.nwv; j++) {
                   tap(j, slot);
-                }
-              };
-              switch (d.nwv) {
-                case 2: taps(std::integral_constant<int, 2>{}); break;
-                case 3: taps(std::integral_constant<int, 3>{}); break;
-                case 4: taps(std::integral_constant<int, 4>{}); break;
-                default: {
-                  int slot = slot0;
-                  for (int j = 0; j < d.nwv; j++) {
-                    tap(j, slot);
-                    if (++slot == ng) slot = 0;
-                  }
+                  if (++slot == ng) slot = 0;
                 }
               }
-              uint32_t u[4];
+            }
+            uint32_t u[4];
 #pragma unroll
-              for (int v = 0; v < 4; v++) u[v] = (a[v][0] + (a[v][1] << 8) + (a[v][2] << 16)) >> kPrecisionBits;
-              int c0, c1, c2, c3;
-              size_t e0;
-              if (nchw) {
-                c0 = c1 = c2 = c3 = ln * 256;
-                e0 = ((size_t)ln * out_h + yy) * out_w + 4 * x4;
-              } else {
-                const int m3 = uu % 3;  // (4 * uu) % 3
-                const int n1 = m3 == 2 ? 0 : m3 + 1, n2 = n1 == 2 ? 0 : n1 + 1;
-                c0 = m3 * 256; c1 = n1 * 256; c2 = n2 * 256; c3 = c0;
-                e0 = (size_t)yy * L + 4 * uu;
-              }
-              if (elem == 4) {
-                const uint32_t* l32 = reinterpret_cast<const uint32_t*>(lut);
-                st_global_v4(dimg + e0 * 4, __ldg(l32 + c0 + u[0]), __ldg(l32 + c1 + u[1]), __ldg(l32 + c2 + u[2]),
-                             __ldg(l32 + c3 + u[3]));
-              } else if (elem == 2) {
-                const uint16_t* l16 = reinterpret_cast<const uint16_t*>(lut);
-                const uint32_t lo = __ldg(l16 + c0 + u[0]) | ((uint32_t)__ldg(l16 + c1 + u[1]) << 16);
-                const uint32_t hi = __ldg(l16 + c2 + u[2]) | ((uint32_t)__ldg(l16 + c3 + u[3]) << 16);
-                st_global_v2(dimg + e0 * 2, lo, hi);
-              } else if (elem == 1) {
-                const uint32_t w = __ldg(lut + c0 + u[0]) | ((uint32_t)__ldg(lut + c1 + u[1]) << 8) |
-                                   ((uint32_t)__ldg(lut + c2 + u[2]) << 16) | ((uint32_t)__ldg(lut + c3 + u[3]) << 24);
-                *reinterpret_cast<uint32_t*>(dimg + e0) = w;
-              } else {
-                const uint2* l64 = reinterpret_cast<const uint2*>(lut);
-                const uint2 q0 = __ldg(l64 + c0 + u[0]), q1 = __ldg(l64 + c1 + u[1]);
-                const uint2 q2 = __ldg(l64 + c2 + u[2]), q3 = __ldg(l64 + c3 + u[3]);
-                st_global_v4(dimg + e0 * 8, q0.x, q0.y, q1.x, q1.y);
-                st_global_v4(dimg + e0 * 8 + 16, q2.x, q2.y, q3.x, q3.y);
-              }
+            for (int v = 0; v < 4; v++) u[v] = (a[v][0] + (a[v][1] << 8) + (a[v][2] << 16)) >> kPrecisionBits;
+            const size_t e0 = (size_t)(v_e0 + yy * v_erow);
+            if (elem == 4) {
+              const uint32_t* l32 = reinterpret_cast<const uint32_t*>(lut_s);
+              st_global_v4(dimg + e0 * 4, l32[c0 + u[0]], l32[c1 + u[1]], l32[c2 + u[2]], l32[c0 + u[3]]);
+            } else if (elem == 2) {
+              const uint16_t* l16 = reinterpret_cast<const uint16_t*>(lut_s);
+              const uint32_t lo = l16[c0 + u[0]] | ((uint32_t)l16[c1 + u[1]] << 16);
+              const uint32_t hi = l16[c2 + u[2]] | ((uint32_t)l16[c0 + u[3]] << 16);
+              st_global_v2(dimg + e0 * 2, lo, hi);
+            } else if (elem == 1) {
+              const uint32_t w = lut_s[c0 + u[0]] | ((uint32_t)lut_s[c1 + u[1]] << 8) |
+                                 ((uint32_t)lut_s[c2 + u[2]] << 16) | ((uint32_t)lut_s[c0 + u[3]] << 24);
+              *reinterpret_cast<uint32_t*>(dimg + e0) = w;
+            } else {
+              const uint2* l64 = reinterpret_cast<const uint2*>(lut_s);
+              const uint2 q0 = l64[c0 + u[0]], q1 = l64[c1 + u[1]], q2 = l64[c2 + u[2]], q3 = l64[c0 + u[3]];
+              st_global_v4(dimg + e0 * 8, q0.x, q0.y, q1.x, q1.y);
+              st_global_v4(dimg + e0 * 8 + 16, q2.x, q2.y, q3.x, q3.y);
             }
           }
         } else {  // destination not 16-byte aligned / odd row length: one element at a time
           nready = 1;
           const int yy = yy_next;
-          const int gv0 = vg[2 * yy];
-          int slot0 = slotB - (g_now - gv0);
+          int slot0 = slotB - (g_now - vg_s[2 * yy]);
           if (slot0 < 0) slot0 += ng;
           const uint4* vc = reinterpret_cast<const uint4*>(pool + d.vc_off) + (size_t)yy * d.nwv;
           for (int i = tid; i < L; i += nthreads) {
@@ -802,11 +828,11 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
             int ch;
             if (nchw) { ch = i / out_w; e = ((size_t)ch * out_h + yy) * out_w + (i - ch * out_w); }
             else { ch = i % C; e = (size_t)yy * L + i; }
-            const uint8_t* le = lut + ((size_t)ch * 256 + u) * elem;
-            if (elem == 4) reinterpret_cast<uint32_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint32_t*>(le));
-            else if (elem == 2) reinterpret_cast<uint16_t*>(dimg)[e] = __ldg(reinterpret_cast<const uint16_t*>(le));
-            else if (elem == 1) dimg[e] = __ldg(le);
-            else reinterpret_cast<unsigned long long*>(dimg)[e] = __ldg(reinterpret_cast<const unsigned long long*>(le));
+            const uint8_t* le = lut_s + ((size_t)ch * 256 + u) * elem;
+            if (elem == 4) reinterpret_cast<uint32_t*>(dimg)[e] = *reinterpret_cast<const uint32_t*>(le);
+            else if (elem == 2) reinterpret_cast<uint16_t*>(dimg)[e] = *reinterpret_cast<const uint16_t*>(le);
+            else if (elem == 1) dimg[e] = *le;
+            else reinterpret_cast<unsigned long long*>(dimg)[e] = *reinterpret_cast<const unsigned long long*>(le);
           }
         }
         yy_next += nready;
@@ -964,8 +990,7 @@ static MmaWindows mma_windows(const std::vector<int32_t>& bounds, int W, int out
   return m;
 }
 
-static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc& d, FusedGeom* g) {
-  (void)elem;
+static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc& d, bool allow_mma, FusedGeom* g) {
   if (d.p1_axis != AXIS_H || d.p2_axis != AXIS_V) return false;
   if (!((d.cin == 3 && c == 3) || (d.cin == 1 && c == 1) || (d.cin == 4 && c == 3) ||
         ((d.cin == 3 || d.cin == 4) && c == 1)))
@@ -989,18 +1014,27 @@ static bool fused_geometry(int c, int out_h, int out_w, int elem, const ImgDesc&
   g->mma_nk = 0;
   // IMMA variant: RGB -> RGB, every row 16-byte aligned, windows of at most three 32-pixel k-steps
   static const bool mma_on = !(getenv("TCB_FUSED_MMA") && atoi(getenv("TCB_FUSED_MMA")) == 0);
-  if (mma_on && c == 3 && d.cin == 3 && d.pitch % 16 == 0 && reinterpret_cast<uintptr_t>(d.src) % 16 == 0 &&
+  if (mma_on && allow_mma && c == 3 && d.cin == 3 && d.pitch % 16 == 0 && reinterpret_cast<uintptr_t>(d.src) % 16 == 0 &&
       out_w <= 512) {
     std::vector<int32_t> bh, kh;
     compute_axis_coeffs(d.W, out_w, bh, kh);
     MmaWindows mw = mma_windows(bh, d.W, out_w);
-    if (mw.nk >= 1 && mw.nk <= 3) {
+    int32_t kmax = 0;
+    for (int32_t kv : kh) kmax = std::max(kmax, kv);
+    // the fragments carry 4 * k in three byte planes: every coefficient must stay below 2^22
+    if (mw.nk >= 1 && mw.nk <= 3 && kmax < (1 << kPrecisionBits)) {
       const int stage = (int)round_up((uint64_t)8 * d.pitch + 64, 128);
-      const size_t smem = 128 + (size_t)stage + (size_t)kMmaLines * mw.wp + (size_t)(nwv + 1) * out_w * 3 * 4;
-      const int warps = (mw.ntiles + kMmaTilesPerWarp - 1) / kMmaTilesPerWarp;
+      static const int tpw_env = getenv("TCB_MMA_TPW") ? atoi(getenv("TCB_MMA_TPW")) : 0;
+      // measured on cfg3: two CTAs of 14 warps (TPW 2) 0.428 ms, one CTA of 28 warps (TPW 1) 0.543 ms - the
+      // phases of one CTA do not overlap, so the single-CTA form is kept only as an experiment switch
+      const int tpw = (tpw_env == 1 && mw.ntiles <= 28) ? 1 : 2;
+      const int warps = (mw.ntiles + tpw - 1) / tpw;
+      const size_t smem = 128 + 768 * (size_t)elem + round_up((uint64_t)out_h * 8, 128) + (size_t)(tpw == 1 ? 2 : 1) * stage +
+                          (size_t)kMmaLines * mw.wp + (size_t)(nwv + 1) * out_w * 3 * 4;
       if (smem <= kFusedMaxSmem) {
         g->mma_nk = mw.nk; g->mma_wp = mw.wp;
-        g->nw_class = 100 + 2 * mw.nk + (warps > 14 ? 1 : 0);
+        // class = 100 + 4 * k-steps + (one tile per warp: 2) + (more than 14 / 28 warps: 1)
+        g->nw_class = 100 + 4 * mw.nk + (tpw == 1 ? 2 : 0) + (tpw == 2 && warps > 14 ? 1 : 0);
         g->stage_bytes = stage;
         g->threads = warps * 32;
         g->smem = smem;
@@ -1037,7 +1071,7 @@ static const FusedGeom& cached_geometry(Plan& p, const ImgDesc& d) {
   auto it = p.geom_cache.find(key);
   if (it == p.geom_cache.end()) {
     FusedGeom g;
-    g.ok = fused_geometry(p.c, p.out_h, p.out_w, p.elem, d, &g);
+    g.ok = fused_geometry(p.c, p.out_h, p.out_w, p.elem, d, !p.no_mma, &g);
     it = p.geom_cache.emplace(key, g).first;
   }
   return it->second;
@@ -1061,13 +1095,16 @@ static int with_kernel(int cls, int c, bool big, F&& f) {
     return c == 3 ? f(k_preprocess_fused<NWv, 3, false>) : f(k_preprocess_fused<NWv, 1, false>);
   switch (cls) {
     TCB_K(2) TCB_K(3) TCB_K(4) TCB_K(5) TCB_K(6) TCB_K(8) TCB_K(10) TCB_K(12) TCB_K(16)
-    // IMMA variant: 100 + 2 * k-steps + (more than 14 warps)
-    case 102: return f(k_preprocess_fused_mma<1, 14>);
-    case 103: return f(k_preprocess_fused_mma<1, 32>);
-    case 104: return f(k_preprocess_fused_mma<2, 14>);
-    case 105: return f(k_preprocess_fused_mma<2, 32>);
-    case 106: return f(k_preprocess_fused_mma<3, 14>);
-    case 107: return f(k_preprocess_fused_mma<3, 32>);
+    // IMMA variant: 100 + 4 * k-steps + (one tile per warp: 2) + (two tiles per warp, more than 14 warps: 1)
+    case 104: return f(k_preprocess_fused_mma<1, 2, 14>);
+    case 105: return f(k_preprocess_fused_mma<1, 2, 32>);
+    case 106: return f(k_preprocess_fused_mma<1, 1, 28>);
+    case 108: return f(k_preprocess_fused_mma<2, 2, 14>);
+    case 109: return f(k_preprocess_fused_mma<2, 2, 32>);
+    case 110: return f(k_preprocess_fused_mma<2, 1, 28>);
+    case 112: return f(k_preprocess_fused_mma<3, 2, 14>);
+    case 113: return f(k_preprocess_fused_mma<3, 2, 32>);
+    case 114: return f(k_preprocess_fused_mma<3, 1, 28>);
     default: return set_error(TCB_ERR_INTERNAL, "bad coefficient class %d", cls);
   }
 #undef TCB_K
@@ -1120,7 +1157,7 @@ int fused_prepare(Plan& p) {
   fp->desc.resize(p.n);
   std::vector<int32_t> pool;
   std::map<std::pair<int, int>, std::array<int32_t, 3>> htab;   // (W, class) -> hc_off, hw0_off, hperm_off
-  std::map<int, std::array<int32_t, 4>> vtab;                    // H -> vc_off, vg_off, vb_off, nwv
+  std::map<int, std::array<int32_t, 5>> vtab;                    // H -> vc_off, vg_off, vb_off, nwv, vq_off
   auto align4 = [&]() { while (pool.size() % 4) pool.push_back(0); };
   for (int i = 0; i < p.n; i++) {
     const ImgDesc& d = p.h_desc[i];
@@ -1154,7 +1191,7 @@ int fused_prepare(Plan& p) {
                     const int x = mw.start[nt] + 32 * kstep + 16 * half + 4 * (ln & 3) + bi;
                     const int t = x - xmin;
                     if (t >= 0 && t < cnt) {
-                      const uint32_t kv = (uint32_t)k[(size_t)col * ks + t];
+                      const uint32_t kv = 4u * (uint32_t)k[(size_t)col * ks + t];  // 4k < 2^24: see the kernel's epilogue
                       word |= ((kv >> (8 * pl)) & 0xffu) << (8 * bi);
                     }
                   }
@@ -1181,7 +1218,7 @@ int fused_prepare(Plan& p) {
       std::vector<int32_t> b, k, packed, first, last;
       const int ks = compute_axis_coeffs(d.H, p.out_h, b, k);
       const int nwv = pack_axis(b, k, ks, p.out_h, 0, packed, first, &last);
-      std::array<int32_t, 4> e;
+      std::array<int32_t, 5> e;
       align4(); e[0] = (int32_t)pool.size();  // [out_h][nwv] x (k0, k1, k2, 0): one 128-bit load per tap word
       for (size_t t = 0; t + 2 < packed.size(); t += 3) {
         pool.push_back(packed[t]); pool.push_back(packed[t + 1]); pool.push_back(packed[t + 2]); pool.push_back(0);
@@ -1190,10 +1227,15 @@ int fused_prepare(Plan& p) {
       for (int o = 0; o < p.out_h; o++) { pool.push_back(first[o]); pool.push_back(last[o]); }
       align4(); e[2] = (int32_t)pool.size(); pool.insert(pool.end(), b.begin(), b.end());
       e[3] = nwv;
+      align4(); e[4] = (int32_t)pool.size();
+      for (int st = 0, done = 0; st < (d.H + 7) / 8; st++) {
+        while (done < p.out_h && last[done] <= 2 * st + 1) done++;
+        pool.push_back(done);
+      }
       vtab[d.H] = e;
     }
     f.hc_off = htab[hk][0]; f.hw0_off = htab[hk][1]; f.hperm_off = htab[hk][2];
-    f.vc_off = vtab[d.H][0]; f.vg_off = vtab[d.H][1]; f.vb_off = vtab[d.H][2];
+    f.vc_off = vtab[d.H][0]; f.vg_off = vtab[d.H][1]; f.vb_off = vtab[d.H][2]; f.vq_off = vtab[d.H][4];
     FusedClass& fc = fp->cls[g.nw_class];
     fc.images.push_back(i);
     fc.smem = std::max(fc.smem, g.smem);
@@ -1214,6 +1256,9 @@ int fused_prepare(Plan& p) {
     });
     if (rc) { delete fp; return rc; }
     per_sm = std::max(per_sm, 1);
+    if (getenv("TCB_DEBUG"))
+      fprintf(stderr, "[tcb] fused class %d: %zu images, %d threads, %zu B smem, %d CTAs/SM resident\n", kv.first,
+              fc.images.size(), fc.threads, fc.smem, per_sm);
     if (per_sm_cap > 0) per_sm = per_sm_cap;
     partition_class(p, *fp, fc, per_sm * sms);
     fc.items_off = allitems.size();
@@ -1258,6 +1303,9 @@ bool fused_accepts(Plan& p, int i, const uint8_t* src, int pitch) {
   const FusedGeom g = cached_geometry(p, t);
   if (!g.ok) return false;
   const auto it = fp->cls.find(g.nw_class);
+  if (getenv("TCB_DEBUG"))
+    fprintf(stderr, "[tcb] fused_accepts image %d: class %d (plan %d), smem %zu (launch %zu)\n", i, g.nw_class,
+            fp->desc[i].nw, g.smem, it != fp->cls.end() ? it->second.smem : (size_t)0);
   return it != fp->cls.end() && g.nw_class == fp->desc[i].nw && g.smem <= it->second.smem;
 }
 

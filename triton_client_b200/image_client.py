@@ -93,7 +93,17 @@ class PreprocessPlan:
         """Enqueue the batch: src_ptrs[i] is the device address of image i's first pixel."""
         imgs = self._ensure(src_ptrs)
         s = stream_ptr(self.device) if stream is None else stream
-        _lib.check(_lib.lib.TcbPreprocessPlanRun(self._plan, imgs, dst_ptr, int(dst_capacity), s))
+        rc = _lib.lib.TcbPreprocessPlanRun(self._plan, imgs, dst_ptr, int(dst_capacity), s)
+        if rc == _lib.TCB_ERR_UNSUPPORTED and imgs is not None:
+            # the new pointers / pitches no longer fit the launch chosen at creation (e.g. rows lost the
+            # 16-byte alignment the IMMA kernel needs): build the plan again for these sources
+            _lib.check(_lib.lib.TcbStreamSync(self.device, s))  # nothing of the old plan may still be running
+            _lib.lib.TcbPreprocessPlanDestroy(self._plan)
+            self._plan = ctypes.c_void_p()
+            self._created = False
+            self._ensure(src_ptrs)
+            rc = _lib.lib.TcbPreprocessPlanRun(self._plan, None, dst_ptr, int(dst_capacity), s)
+        _lib.check(rc)
 
     def close(self):
         if self._created:
@@ -221,26 +231,21 @@ class HostBatchPipeline:
         flat = images.reshape(-1)
         if flat.dtype != np.uint8 or flat.size != self.n * self.img_bytes:
             raise ValueError("images must be uint8 with %d bytes in total" % (self.n * self.img_bytes))
-        piece = max(self.bounds[k + 1] - self.bounds[k] for k in range(len(self.plans))) * self.img_bytes
-        if getattr(self, "_pin", None) is None:
-            self._pin = [torch.empty(piece, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
-            self._pin_np = [t.numpy() for t in self._pin]
-            self._pin_free = [torch.cuda.Event() for _ in range(2)]
+        if getattr(self, "_pin_out", None) is None:
             self._pin_out = torch.empty(self.n * self.out_bytes_per_image, dtype=torch.uint8, pin_memory=True)
         cur = torch.cuda.current_stream(self.device)
         self.s_in.wait_stream(cur)
         self.s_out.wait_stream(cur)
         base = self.stage.data_ptr()
+        src_ptr = flat.ctypes.data
         for k, plan in enumerate(self.plans):
             i0, i1 = self.bounds[k], self.bounds[k + 1]
             nb = (i1 - i0) * self.img_bytes
-            b = k & 1
-            if k >= 2:
-                self._pin_free[b].synchronize()  # the DMA that last read this staging buffer is done
-            np.copyto(self._pin_np[b][:nb], flat[i0 * self.img_bytes:i1 * self.img_bytes])
-            _lib.check(_lib.lib.TcbMemcpy(self.device, base + i0 * self.img_bytes, self._pin[b].data_ptr(), nb,
+            # TcbMemcpy sees pageable memory and goes through the library's pinned ring: several host
+            # threads fill one ring slot while the DMA engine drains the previous one (staging.cu); it
+            # returns when the source has been consumed, the kernel of this piece is queued behind it
+            _lib.check(_lib.lib.TcbMemcpy(self.device, base + i0 * self.img_bytes, src_ptr + i0 * self.img_bytes, nb,
                                           self.s_in.cuda_stream, 0))
-            self._pin_free[b].record(self.s_in)
             self.events[k].record(self.s_in)
             self.s_out.wait_event(self.events[k])
             ob = (i1 - i0) * self.out_bytes_per_image

@@ -64,7 +64,9 @@ def set_shared_memory_region(cuda_shm_handle, input_values, offset=0):
         offset_current = int(offset)
         keep = []  # host buffers must outlive the asynchronous copies
         for input_value in input_values:
-            input_value = np.ascontiguousarray(input_value).flatten()
+            # the reference's ascontiguousarray(...).flatten() copies the array a second time; a flat
+            # view of the contiguous array holds the same bytes
+            input_value = np.ascontiguousarray(input_value).reshape(-1)
             if input_value.dtype == np.object_:
                 data = input_value.item()
                 src = np.frombuffer(data, dtype=np.uint8)
