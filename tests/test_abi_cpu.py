@@ -132,7 +132,7 @@ def test_argument_validation_without_gpu():
     assert L.TcbPreprocessPlanCreate(*args(layout=0)) == _lib.TCB_ERR_INVALID_ARG
     assert L.TcbPreprocessPlanCreate(*args(elem=3)) == _lib.TCB_ERR_INVALID_ARG
     assert L.TcbPreprocessPlanCreate(*args(h=0)) == _lib.TCB_ERR_INVALID_ARG
-    assert L.TcbPreprocessPlanCreate(*args(path=3)) == _lib.TCB_ERR_INVALID_ARG
+    assert L.TcbPreprocessPlanCreate(*args(path=4)) == _lib.TCB_ERR_INVALID_ARG
     bad = (_lib.TcbImage * 1)(_lib.TcbImage(0, 4, 4, 11, 3))
     assert L.TcbPreprocessPlanCreate(*args(imgs=bad)) == _lib.TCB_ERR_INVALID_ARG
     assert "pitch" in _lib.last_error()
