@@ -145,6 +145,21 @@ def test_roundtrip_edge_lengths():
     _roundtrip([2] * 40000, "zeros")             # more headers per chunk than the per-chunk list holds
 
 
+@pytest.mark.parametrize("kind", ["random", "zeros", "small_ints"])
+def test_roundtrip_long_elements_wide_vote_and_sweep(kind):
+    """Elements longer than the 512-byte entry window: the first vote finds no header, the wider
+    second-chance votes (8 KiB, 128 KiB) or the warp-parallel sweep must repair every chunk. Zeros
+    and small integers are payloads that look like length prefixes (every guess may be wrong)."""
+    rng = np.random.default_rng(11)
+    _roundtrip(np.full(20000, 1024), kind, seed=1)                 # 20 MB of 1 KiB elements: 8 KiB window
+    _roundtrip(rng.integers(513, 8000, 6000), kind, seed=2)        # mixed, all beyond the small window
+    _roundtrip(np.full(700, 40000), kind, seed=3)                  # 128 KiB window
+    _roundtrip(rng.integers(20000, 120000, 300), kind, seed=4)
+    _roundtrip([300000, 12, 700000, 0, 0, 1 << 21, 5, 150000], kind, seed=5)   # beyond every window: sweep
+    _roundtrip(np.concatenate([rng.integers(0, 257, 30000), np.full(50, 100000), rng.integers(0, 257, 30000),
+                               np.full(3000, 2000)]), kind, seed=6)  # short / very long / short / medium
+
+
 def test_truncated_streams_raise_struct_error():
     from triton_client_b200 import utils as u
 

@@ -7,14 +7,16 @@
 // b"\x00\x00" + two bytes -> float32).
 //
 // Two streaming kernels, HBM-bound: 6 bytes of traffic per element either way. A thread moves
-// eight elements per step: two 128-bit loads + one 128-bit store (pack) or one load + two stores
-// (expand). Unaligned heads and tails are handled element-wise by the first CTA.
+// four elements per step: one 128-bit load + one 64-bit store (pack) or the reverse (expand). Unaligned heads and tails are handled element-wise by the first CTA.
+#include <algorithm>
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace tcb {
 
 constexpr int kBfThreads = 256;
-constexpr int kBfUnroll = 4;  // 8-element groups in flight per thread
+constexpr int kBfUnroll = 8;  // 4-element groups in flight per thread
 
 __device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
   uint4 v;
@@ -40,55 +42,30 @@ __device__ __forceinline__ uint32_t pack2(uint32_t lo, uint32_t hi) {
   return __byte_perm(quiet(lo), quiet(hi), 0x7632);
 }
 
+__device__ __forceinline__ uint2 ld_stream_v2(const void* p) {
+  uint2 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_stream_v2(void* p, uint2 v) {
+  asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+// A thread moves groups of FOUR elements: 16 bytes of float32 <-> 8 bytes of bfloat16, so that both
+// the loads and the stores of a warp are one contiguous run (512 / 256 bytes). (With eight elements
+// per thread the expand kernel's two 16-byte stores were 32 bytes apart from lane to lane and every
+// store instruction filled only half of each sector it touched: 59 % of the copy rate.)
+constexpr int kBfGroup = 4;
+
 // src: n float32 (4-byte aligned), dst: n uint16 (2-byte aligned). `head` elements are peeled so
-// that the vector body reads 16-byte aligned float4 pairs; the destination of the body is then
-// 16-byte aligned iff dst_vec_ok (decided on the host).
+// that the vector body reads 16-byte aligned float4s; DST_VEC: the body's destination is 8-byte
+// aligned too (decided on the host).
 template <bool DST_VEC>
 __global__ void __launch_bounds__(kBfThreads)
 k_bf16_pack(const uint32_t* __restrict__ src, uint16_t* __restrict__ dst, unsigned long long n,
             unsigned int head) {
-  const unsigned long long groups = (n - head) / 8;
-  const unsigned long long body_end = head + groups * 8;
-  const uint4* s4 = reinterpret_cast<const uint4*>(src + head);
-  const unsigned long long stride = (unsigned long long)gridDim.x * kBfThreads;
-  for (unsigned long long g0 = (unsigned long long)blockIdx.x * kBfThreads + threadIdx.x; g0 < groups;
-       g0 += stride * kBfUnroll) {
-    uint4 a[kBfUnroll], b[kBfUnroll];
-#pragma unroll
-    for (int u = 0; u < kBfUnroll; u++) {
-      const unsigned long long g = g0 + u * stride;
-      if (g < groups) { a[u] = ld_stream_v4(s4 + 2 * g); b[u] = ld_stream_v4(s4 + 2 * g + 1); }
-    }
-#pragma unroll
-    for (int u = 0; u < kBfUnroll; u++) {
-      const unsigned long long g = g0 + u * stride;
-      if (g >= groups) continue;
-      const uint4 o = make_uint4(pack2(a[u].x, a[u].y), pack2(a[u].z, a[u].w), pack2(b[u].x, b[u].y),
-                                 pack2(b[u].z, b[u].w));
-      uint16_t* d = dst + head + 8 * g;
-      if (DST_VEC) {
-        st_stream_v4(d, o);
-      } else {  // destination only 2-byte aligned relative to the source: halfword stores
-        const uint32_t w[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-        for (int k = 0; k < 4; k++) { d[2 * k] = (uint16_t)w[k]; d[2 * k + 1] = (uint16_t)(w[k] >> 16); }
-      }
-    }
-  }
-  if (blockIdx.x == 0) {  // head and tail, element-wise
-    for (unsigned long long i = threadIdx.x; i < head; i += kBfThreads) dst[i] = (uint16_t)(quiet(src[i]) >> 16);
-    for (unsigned long long i = body_end + threadIdx.x; i < n; i += kBfThreads) dst[i] = (uint16_t)(quiet(src[i]) >> 16);
-  }
-}
-
-// src: n uint16, dst: n float32 patterns (bf16 << 16). `head` elements peeled so that the body
-// reads 16-byte aligned vectors; DST_VEC: the body's destination is 16-byte aligned too.
-template <bool DST_VEC>
-__global__ void __launch_bounds__(kBfThreads)
-k_bf16_expand(const uint16_t* __restrict__ src, uint32_t* __restrict__ dst, unsigned long long n,
-              unsigned int head) {
-  const unsigned long long groups = (n - head) / 8;
-  const unsigned long long body_end = head + groups * 8;
+  const unsigned long long groups = (n - head) / kBfGroup;
+  const unsigned long long body_end = head + groups * kBfGroup;
   const uint4* s4 = reinterpret_cast<const uint4*>(src + head);
   const unsigned long long stride = (unsigned long long)gridDim.x * kBfThreads;
   for (unsigned long long g0 = (unsigned long long)blockIdx.x * kBfThreads + threadIdx.x; g0 < groups;
@@ -103,17 +80,50 @@ k_bf16_expand(const uint16_t* __restrict__ src, uint32_t* __restrict__ dst, unsi
     for (int u = 0; u < kBfUnroll; u++) {
       const unsigned long long g = g0 + u * stride;
       if (g >= groups) continue;
-      const uint4 lo = make_uint4(quiet(a[u].x << 16), quiet(a[u].x & 0xffff0000u), quiet(a[u].y << 16),
-                                  quiet(a[u].y & 0xffff0000u));
-      const uint4 hi = make_uint4(quiet(a[u].z << 16), quiet(a[u].z & 0xffff0000u), quiet(a[u].w << 16),
-                                  quiet(a[u].w & 0xffff0000u));
-      uint32_t* d = dst + head + 8 * g;
+      const uint2 o = make_uint2(pack2(a[u].x, a[u].y), pack2(a[u].z, a[u].w));
+      uint16_t* d = dst + head + kBfGroup * g;
       if (DST_VEC) {
-        st_stream_v4(d, lo);
-        st_stream_v4(d + 4, hi);
+        st_stream_v2(d, o);
+      } else {  // destination only 2-byte aligned relative to the source: halfword stores
+        d[0] = (uint16_t)o.x; d[1] = (uint16_t)(o.x >> 16); d[2] = (uint16_t)o.y; d[3] = (uint16_t)(o.y >> 16);
+      }
+    }
+  }
+  if (blockIdx.x == 0) {  // head and tail, element-wise
+    for (unsigned long long i = threadIdx.x; i < head; i += kBfThreads) dst[i] = (uint16_t)(quiet(src[i]) >> 16);
+    for (unsigned long long i = body_end + threadIdx.x; i < n; i += kBfThreads) dst[i] = (uint16_t)(quiet(src[i]) >> 16);
+  }
+}
+
+// src: n uint16, dst: n float32 patterns (bf16 << 16). `head` elements peeled so that the body
+// reads 8-byte aligned vectors; DST_VEC: the body's destination is 16-byte aligned too.
+template <bool DST_VEC>
+__global__ void __launch_bounds__(kBfThreads)
+k_bf16_expand(const uint16_t* __restrict__ src, uint32_t* __restrict__ dst, unsigned long long n,
+              unsigned int head) {
+  const unsigned long long groups = (n - head) / kBfGroup;
+  const unsigned long long body_end = head + groups * kBfGroup;
+  const uint2* s2 = reinterpret_cast<const uint2*>(src + head);
+  const unsigned long long stride = (unsigned long long)gridDim.x * kBfThreads;
+  for (unsigned long long g0 = (unsigned long long)blockIdx.x * kBfThreads + threadIdx.x; g0 < groups;
+       g0 += stride * kBfUnroll) {
+    uint2 a[kBfUnroll];
+#pragma unroll
+    for (int u = 0; u < kBfUnroll; u++) {
+      const unsigned long long g = g0 + u * stride;
+      if (g < groups) a[u] = ld_stream_v2(s2 + g);
+    }
+#pragma unroll
+    for (int u = 0; u < kBfUnroll; u++) {
+      const unsigned long long g = g0 + u * stride;
+      if (g >= groups) continue;
+      const uint4 o = make_uint4(quiet(a[u].x << 16), quiet(a[u].x & 0xffff0000u), quiet(a[u].y << 16),
+                                 quiet(a[u].y & 0xffff0000u));
+      uint32_t* d = dst + head + kBfGroup * g;
+      if (DST_VEC) {
+        st_stream_v4(d, o);
       } else {
-        d[0] = lo.x; d[1] = lo.y; d[2] = lo.z; d[3] = lo.w;
-        d[4] = hi.x; d[5] = hi.y; d[6] = hi.z; d[7] = hi.w;
+        d[0] = o.x; d[1] = o.y; d[2] = o.z; d[3] = o.w;
       }
     }
   }
@@ -124,10 +134,11 @@ k_bf16_expand(const uint16_t* __restrict__ src, uint32_t* __restrict__ dst, unsi
 }
 
 static unsigned bf16_grid(int device, unsigned long long groups) {
-  // enough CTAs to fill the GPU 8 deep; grid-stride covers the rest
+  // one CTA per 8 K elements up to 64 per SM; grid-stride covers the rest
   const unsigned long long want = (groups + (unsigned long long)kBfThreads * kBfUnroll - 1) /
                                   ((unsigned long long)kBfThreads * kBfUnroll);
-  const unsigned long long cap = (unsigned long long)sm_count(device) * 8;
+  static const int per_sm = getenv("TCB_BF16_CTAS_PER_SM") ? atoi(getenv("TCB_BF16_CTAS_PER_SM")) : 64;  // one pass, no grid-stride tail (8: 0.75-0.80 of the copy rate, 64: 0.83)
+  const unsigned long long cap = (unsigned long long)sm_count(device) * per_sm;
   return (unsigned)std::max<unsigned long long>(1, std::min(want, cap));
 }
 
@@ -154,8 +165,8 @@ int TcbBf16Serialize(int device_id, const void* src_f32_dev, uint64_t n_elements
   // elements to peel so that the source body is 16-byte aligned
   unsigned head = (unsigned)(((16 - (reinterpret_cast<uintptr_t>(src) & 15)) & 15) / 4);
   if (head > n_elements) head = (unsigned)n_elements;
-  const bool dst_vec = (reinterpret_cast<uintptr_t>(dst + head) & 15) == 0;
-  const unsigned grid = bf16_grid(device_id, (n_elements - head) / 8);
+  const bool dst_vec = (reinterpret_cast<uintptr_t>(dst + head) & 7) == 0;
+  const unsigned grid = bf16_grid(device_id, (n_elements - head) / kBfGroup);
   if (dst_vec) k_bf16_pack<true><<<grid, kBfThreads, 0, s>>>(src, dst, n_elements, head);
   else k_bf16_pack<false><<<grid, kBfThreads, 0, s>>>(src, dst, n_elements, head);
   count_launch();
@@ -180,10 +191,10 @@ int TcbBf16Deserialize(int device_id, const void* src_dev, uint64_t src_bytes, v
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const uint16_t* src = static_cast<const uint16_t*>(src_dev);
   uint32_t* dst = static_cast<uint32_t*>(dst_f32_dev);
-  unsigned head = (unsigned)(((16 - (reinterpret_cast<uintptr_t>(src) & 15)) & 15) / 2);
+  unsigned head = (unsigned)(((8 - (reinterpret_cast<uintptr_t>(src) & 7)) & 7) / 2);
   if (head > n) head = (unsigned)n;
   const bool dst_vec = (reinterpret_cast<uintptr_t>(dst + head) & 15) == 0;
-  const unsigned grid = bf16_grid(device_id, (n - head) / 8);
+  const unsigned grid = bf16_grid(device_id, (n - head) / kBfGroup);
   if (dst_vec) k_bf16_expand<true><<<grid, kBfThreads, 0, s>>>(src, dst, n, head);
   else k_bf16_expand<false><<<grid, kBfThreads, 0, s>>>(src, dst, n, head);
   count_launch();

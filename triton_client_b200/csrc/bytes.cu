@@ -16,6 +16,10 @@
 //   chunk, which makes the result exact; any mismatch (elements longer than the window,
 //   adversarial payloads) is repaired by a sequential sweep. A scan of per-chunk counts gives
 //   element indices; payloads are then gathered with the same output-centric copy.
+#include <cstdlib>
+#include <utility>
+#include <vector>
+
 #include "common.cuh"
 
 namespace tcb {
@@ -731,7 +735,7 @@ k_bytes_serialize(const uint8_t* __restrict__ payload, const void* __restrict__ 
 // =================================================================================================
 constexpr int kDesChunk = 16384;   // bytes of stream per chunk
 constexpr int kDesWindow = 512;    // look-behind window for the entry guess
-constexpr int kDesWarps = 4;       // warps per CTA of k_des_speculate; one warp = 32 consecutive chunks
+constexpr int kDesWarps = 4;       // warps per CTA of k_des_chase (one lane per chunk)
 constexpr int kDesThreads = kDesWarps * 32;
 constexpr int kDesListCap = 512;   // header positions recorded per chunk (uint16, chunk-relative)
 constexpr unsigned long long kNoGuess = ~0ull;
@@ -767,109 +771,160 @@ __device__ __forceinline__ uint32_t ldg_u32_unaligned(const uint8_t* __restrict_
   return __funnelshift_r(lo, __ldg(w + 1), sh);
 }
 
-// Speculative chunk chase. One warp owns 32 consecutive chunks:
-//   1. entry guess, warp-cooperative, one chunk at a time: the 32 lanes chase from every byte of
-//      the chunk's 512-byte look-behind window (consecutive candidates -> coalesced loads) to the
-//      chunk start and vote on where they land; the plurality (ties: smallest offset) is the guess;
-//   2. main chase, lane-parallel: lane l follows the chain of chunk l straight from global memory,
-//      so one warp instruction advances 32 independent chains (a per-CTA serial chase spent 31 of
-//      32 lanes idle and made this kernel instruction-bound), recording header positions.
+// Speculative chunk chase, two kernels.
+//   k_des_vote : one WARP per chunk guesses the chunk's entry header. The 32 lanes chase from every
+//      byte of the chunk's 512-byte look-behind window (staged in shared memory with one coalesced
+//      round trip) to the chunk start and vote on where they land; the plurality (ties: smallest
+//      offset) is the guess. Chunks are independent, so the grid is as wide as the stream is long -
+//      the first version ran the 32 votes of a warp's chunks one after the other in front of the
+//      chase, and that serial prologue was a third of the whole deserialise.
+//   k_des_chase: one LANE per chunk follows the chain of its chunk straight from global memory from
+//      the guessed entry, recording header positions: a warp instruction advances 32 independent
+//      chains.
 // Exactness does not depend on the guess: k_des_verify checks entry[k] == exit[k-1] for all k.
 // stream4 = stream rounded down to a 4-byte boundary, bias = stream - stream4 (0..3).
-__global__ void __launch_bounds__(kDesThreads)
-k_des_speculate(const uint8_t* __restrict__ stream4, unsigned int bias, unsigned long long S,
-                unsigned long long K, DesArrays A) {
-  __shared__ unsigned int s_votes[kDesWarps][kDesWindow];
-  __shared__ unsigned int s_win[kDesWarps][kDesWindow / 4 + 4];  // look-behind window (+ 16 bytes) of one chunk
+constexpr int kVoteWarps = 8;
+constexpr int kWinWords = kDesWindow / 4 + 4;  // look-behind window + 16 bytes
+
+__global__ void __launch_bounds__(kVoteWarps * 32)
+k_des_vote(const uint8_t* __restrict__ stream4, unsigned int bias, unsigned long long S,
+           unsigned long long K, DesArrays A) {
+  __shared__ unsigned int s_votes[kVoteWarps][kDesWindow];
+  __shared__ unsigned int s_win[kVoteWarps][kWinWords];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const unsigned long long kbase = ((unsigned long long)blockIdx.x * kDesWarps + warp) * 32;
-  if (kbase >= K) return;
+  const unsigned long long k = (unsigned long long)blockIdx.x * kVoteWarps + warp;
+  if (k >= K) return;
+  if (k == 0) {
+    if (lane == 0) A.g[0] = 0;
+    return;
+  }
   unsigned int* votes = s_votes[warp];
   unsigned int* win = s_win[warp];
-  auto load_len = [&](unsigned long long pos) { return ldg_u32_unaligned(stream4, pos + bias); };
+  const unsigned long long c0 = k * kDesChunk;
   const unsigned long long S4 = (S + bias + 3) >> 2;  // words of stream4 that hold stream bytes
-  constexpr int kWinWords = kDesWindow / 4 + 4;
-  constexpr int kWinPerLane = (kWinWords + 31) / 32;
-  // The window of a chunk is fetched with ONE coalesced round trip (and the next chunk's window
-  // while this one is voted on): read word by word from global memory, every 32-byte step of the
-  // candidate loop was a fresh DRAM sector and the vote cost two thirds of the kernel.
-  auto fetch_window = [&](unsigned long long k, unsigned int (&w)[kWinPerLane]) {
-    const unsigned long long w0 = (k * kDesChunk - kDesWindow) >> 2;  // first word (stream4 is 4-byte aligned)
-#pragma unroll
-    for (int i = 0; i < kWinPerLane; i++) {
-      const unsigned long long wi = w0 + (unsigned long long)i * 32 + lane;
-      w[i] = (i * 32 + lane < kWinWords && wi < S4) ? __ldg(reinterpret_cast<const uint32_t*>(stream4) + wi) : 0u;
-    }
-  };
-  unsigned int wnext[kWinPerLane];
-#pragma unroll
-  for (int i = 0; i < kWinPerLane; i++) wnext[i] = 0;
-  if (kbase + (kbase == 0 ? 1 : 0) < K) fetch_window(kbase + (kbase == 0 ? 1 : 0), wnext);
-
-  unsigned long long my_g = kNoGuess;
-  for (int j = 0; j < 32; j++) {
-    const unsigned long long k = kbase + j;
-    if (k >= K) break;
-    if (k == 0) {
-      if (lane == j) my_g = 0;
-      continue;
-    }
-    const unsigned long long c0 = k * kDesChunk;
-    // publish this chunk's window, start the next one's loads
-#pragma unroll
-    for (int i = 0; i < kWinPerLane; i++)
-      if (i * 32 + lane < kWinWords) win[i * 32 + lane] = wnext[i];
-    for (int i = lane; i < kDesWindow; i += 32) votes[i] = 0;
-    if (j + 1 < 32 && k + 1 < K) fetch_window(k + 1, wnext);
-    __syncwarp();
-    // window byte b (0 = stream position c0 - kDesWindow) sits at byte b + bias of win[]
-    auto win_len = [&](unsigned int b) {
-      const unsigned int q = b + bias;
-      const unsigned int lo = win[q >> 2];
-      const unsigned int sh = (q & 3) * 8;
-      return sh ? __funnelshift_r(lo, win[(q >> 2) + 1], sh) : lo;
-    };
-    const unsigned long long wbase = c0 - kDesWindow;
-    for (int it = 0; it < kDesWindow / 32; it++) {
-      unsigned long long pos = wbase + it * 32 + lane;
-      bool ok = true;
-      while (pos < c0) {
-        if (pos + 4 > S) { ok = false; break; }
-        const unsigned long long nx = pos + 4 + win_len((unsigned int)(pos - wbase));
-        if (nx > S) { ok = false; break; }
-        pos = nx;
-      }
-      if (ok && pos - c0 < kDesWindow) atomicAdd(&votes[pos - c0], 1u);
-    }
-    __syncwarp();
-    unsigned int best = 0;
-    for (int i = lane; i < kDesWindow; i += 32) {
-      const unsigned int v = votes[i];
-      if (v) best = max(best, (v << 16) | (unsigned int)(kDesWindow - 1 - i));
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
-    if (lane == j) my_g = best ? c0 + (kDesWindow - 1 - (best & 0xffffu)) : kNoGuess;
-    __syncwarp();
+  const unsigned long long w0 = (c0 - kDesWindow) >> 2;  // first window word (stream4 is 4-byte aligned)
+  for (int i = lane; i < kWinWords; i += 32) {
+    const unsigned long long wi = w0 + i;
+    win[i] = wi < S4 ? __ldg(reinterpret_cast<const uint32_t*>(stream4) + wi) : 0u;
   }
-  // main chase: lane -> chunk kbase + lane
-  const unsigned long long k = kbase + lane;
+  for (int i = lane; i < kDesWindow; i += 32) votes[i] = 0;
+  __syncwarp();
+  // window byte b (0 = stream position c0 - kDesWindow) sits at byte b + bias of win[]
+  auto win_len = [&](unsigned int b) {
+    const unsigned int q = b + bias;
+    const unsigned int lo = win[q >> 2];
+    const unsigned int sh = (q & 3) * 8;
+    return sh ? __funnelshift_r(lo, win[(q >> 2) + 1], sh) : lo;
+  };
+  const unsigned long long wbase = c0 - kDesWindow;
+  for (int it = 0; it < kDesWindow / 32; it++) {
+    unsigned long long pos = wbase + it * 32 + lane;
+    bool ok = true;
+    while (pos < c0) {
+      if (pos + 4 > S) { ok = false; break; }
+      const unsigned long long nx = pos + 4 + win_len((unsigned int)(pos - wbase));
+      if (nx > S) { ok = false; break; }
+      pos = nx;
+    }
+    if (ok && pos - c0 < kDesWindow) atomicAdd(&votes[pos - c0], 1u);
+  }
+  __syncwarp();
+  unsigned int best = 0;
+  for (int i = lane; i < kDesWindow; i += 32) {
+    const unsigned int v = votes[i];
+    if (v) best = max(best, (v << 16) | (unsigned int)(kDesWindow - 1 - i));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if (lane == 0) A.g[k] = best ? c0 + (kDesWindow - 1 - (best & 0xffffu)) : kNoGuess;
+}
+
+constexpr unsigned int kErrRechase = 2;  // A.err value: a wide vote replaced this chunk's guess, chase it again
+
+__global__ void __launch_bounds__(kDesThreads)
+k_des_chase(const uint8_t* __restrict__ stream4, unsigned int bias, unsigned long long S,
+            unsigned long long K, DesArrays A, int only_flagged) {
+  const unsigned long long k = (unsigned long long)blockIdx.x * kDesThreads + threadIdx.x;
   if (k >= K) return;
+  if (only_flagged && A.err[k] != kErrRechase) return;
   const unsigned long long c0 = k * kDesChunk, c1 = min(c0 + kDesChunk, S);
+  const unsigned long long my_g = A.g[k];
   unsigned long long pos = my_g;
   unsigned int n = 0, err = 0;
   unsigned short* list = A.list + k * kDesListCap;
   if (my_g != kNoGuess) {
     while (pos < c1) {
       if (pos + 4 > S) { err = 1; break; }
-      const unsigned long long nx = pos + 4 + load_len(pos);
+      const unsigned long long nx = pos + 4 + ldg_u32_unaligned(stream4, pos + bias);
       if (nx > S) { err = 1; break; }
       if (n < kDesListCap) list[n] = (unsigned short)(pos - c0);
       n++;
       pos = nx;
     }
   }
-  A.g[k] = my_g; A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
+  A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
+}
+
+// Second-chance vote for chunks whose first guess failed verification, with a look-behind window of
+// `window` bytes instead of 512: elements longer than the small window leave it without a single
+// header, and every such chunk used to fall to the sequential sweep (130 ms for 256 MiB of 1 KiB
+// elements). One warp per failed chunk; candidates are read straight from global memory (the window
+// does not fit shared memory), chains are cut after kWideHops hops, landing positions are counted in
+// a small per-warp hash table. The result is again only a guess - verification decides.
+constexpr int kWideHops = 96;
+constexpr int kWideSlots = 128;
+
+__global__ void __launch_bounds__(kVoteWarps * 32)
+k_des_vote_wide(const uint8_t* __restrict__ stream4, unsigned int bias, unsigned long long S,
+                unsigned long long K, DesArrays A, const unsigned long long* __restrict__ hdr,
+                unsigned long long window) {
+  __shared__ unsigned long long s_key[kVoteWarps][kWideSlots];
+  __shared__ unsigned int s_cnt[kVoteWarps][kWideSlots];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned long long k = (unsigned long long)blockIdx.x * kVoteWarps + warp;
+  if (k >= K || k == 0 || k < hdr[DW_FIRST_MISMATCH]) return;
+  if (A.g[k] == A.x[k - 1] && A.g[k] != kNoGuess) return;  // consistent with its predecessor so far: keep
+  unsigned long long* key = s_key[warp];
+  unsigned int* cnt = s_cnt[warp];
+  for (int i = lane; i < kWideSlots; i += 32) { key[i] = ~0ull; cnt[i] = 0; }
+  __syncwarp();
+  const unsigned long long c0 = k * kDesChunk;
+  const unsigned long long wbase = c0 > window ? c0 - window : 0;
+  for (unsigned long long p0 = wbase; p0 < c0; p0 += 32) {
+    unsigned long long pos = p0 + lane;
+    bool ok = pos < c0;
+    for (int hop = 0; ok && pos < c0; hop++) {
+      if (hop >= kWideHops || pos + 4 > S) { ok = false; break; }
+      const unsigned long long nx = pos + 4 + ldg_u32_unaligned(stream4, pos + bias);
+      if (nx > S) { ok = false; break; }
+      pos = nx;
+    }
+    if (ok) {  // count the landing position
+      unsigned int h = (unsigned int)((pos * 0x9E3779B97F4A7C15ull) >> 57);  // 7 bits
+      for (int probe = 0; probe < kWideSlots; probe++) {
+        const unsigned long long prev = atomicCAS(&key[h], ~0ull, pos);
+        if (prev == ~0ull || prev == pos) { atomicAdd(&cnt[h], 1u); break; }
+        h = (h + 1) & (kWideSlots - 1);
+      }
+    }
+  }
+  __syncwarp();
+  unsigned int best = 0;
+  unsigned long long best_pos = ~0ull;
+  for (int i = lane; i < kWideSlots; i += 32) {
+    const unsigned int c = cnt[i];
+    if (c > best || (c == best && c > 0 && key[i] < best_pos)) { best = c; best_pos = key[i]; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned int ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const unsigned long long op = __shfl_xor_sync(0xffffffffu, best_pos, o);
+    if (ob > best || (ob == best && op < best_pos)) { best = ob; best_pos = op; }
+  }
+  if (lane == 0) {
+    A.g[k] = best ? best_pos : kNoGuess;
+    A.err[k] = kErrRechase;
+  }
 }
 
 // One chase step straight from global memory (sweep / overflow paths).
@@ -983,50 +1038,65 @@ __global__ void k_des_finalize(unsigned long long S, unsigned long long K, long 
   hdr[DW_FIRST_MISMATCH] = first;
 }
 
-// Sequential repair from the first mismatching chunk: re-chase chunks whose guessed entry was
-// wrong (or missing), pass through chunks that a long element skips. Exact by construction.
+// Sequential repair from the first mismatching chunk (whatever the votes could not settle): lane 0
+// walks the true chain, re-chasing chunks whose guessed entry was wrong; the chunks that a long
+// element skips entirely are filled in by the whole warp at once. Exact by construction.
 __global__ void k_des_sweep(const uint8_t* __restrict__ stream, unsigned long long S,
                             unsigned long long K, long long max_elements, DesArrays A,
                             unsigned long long* hdr) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
   unsigned long long k = hdr[DW_FIRST_MISMATCH];
   unsigned long long count = k < K ? A.base[k] : 0;
   unsigned long long e = k == 0 ? 0 : A.x[k - 1];
   const bool limited = max_elements >= 0;
   const unsigned long long M = limited ? (unsigned long long)max_elements : ~0ull;
-  bool trunc = false, stop = false;
-  hdr[DW_SWEPT] = 1;
-  for (; k < K; k++) {
+  bool stop = false;
+  if (lane == 0) hdr[DW_SWEPT] = 1;
+  while (k < K) {
     const unsigned long long c0 = k * kDesChunk, c1 = min(c0 + kDesChunk, S);
-    if (stop || e >= c1) {  // nothing of the true chain starts in this chunk
-      A.g[k] = e; A.x[k] = e; A.cnt[k] = 0; A.err[k] = 0;
+    if (stop || e >= c1) {  // nothing of the true chain starts in chunks [k, k2): all lanes fill them
+      const unsigned long long k2 = stop ? K : min(K, e / kDesChunk);
+      const unsigned long long kend = max(k2, k + 1);
+      for (unsigned long long kk = k + lane; kk < kend; kk += 32) {
+        A.g[kk] = e; A.x[kk] = e; A.cnt[kk] = 0; A.err[kk] = 0;
+      }
+      k = kend;
       continue;
     }
-    if (A.g[k] == e) {  // the guess was right after all
-      count += A.cnt[k];
-      if (A.err[k] && !(limited && count >= M)) { trunc = true; stop = true; }
-      e = A.x[k];
-      if (limited && count >= M) stop = true;
-      continue;
+    // lane 0 handles the chunk; the outcome is broadcast
+    unsigned long long ne = e, ncount = count;
+    int nstop = 0;
+    if (lane == 0) {
+      if (A.g[k] == e && A.err[k] != kErrRechase) {  // the guess was right after all
+        ncount += A.cnt[k];
+        if (A.err[k] && !(limited && ncount >= M)) nstop = 1;
+        ne = A.x[k];
+        if (limited && ncount >= M) nstop = 1;
+      } else {
+        unsigned long long pos = e;
+        unsigned int n = 0, err = 0;
+        unsigned short* list = A.list + k * kDesListCap;
+        while (pos < c1) {
+          unsigned long long nx;
+          if (!chase_global(stream, S, pos, &nx)) { err = 1; break; }
+          if (n < kDesListCap) list[n] = (unsigned short)(pos - c0);
+          n++;
+          pos = nx;
+          if (limited && count + n >= M) break;
+        }
+        A.g[k] = e; A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
+        ncount += n;
+        ne = pos;
+        if (limited && ncount >= M) { nstop = 1; A.err[k] = 0; }
+        else if (err) nstop = 1;
+      }
     }
-    unsigned long long pos = e;
-    unsigned int n = 0, err = 0;
-    unsigned short* list = A.list + k * kDesListCap;
-    while (pos < c1) {
-      unsigned long long nx;
-      if (!chase_global(stream, S, pos, &nx)) { err = 1; break; }
-      if (n < kDesListCap) list[n] = (unsigned short)(pos - c0);
-      n++;
-      pos = nx;
-      if (limited && count + n >= M) break;
-    }
-    A.g[k] = e; A.x[k] = pos; A.cnt[k] = n; A.err[k] = err;
-    count += n;
-    e = pos;
-    if (limited && count >= M) { stop = true; A.err[k] = 0; }
-    else if (err) { trunc = true; stop = true; }
+    e = __shfl_sync(0xffffffffu, ne, 0);
+    count = __shfl_sync(0xffffffffu, ncount, 0);
+    stop = __shfl_sync(0xffffffffu, nstop, 0) != 0;
+    k++;
   }
-  (void)trunc;  // the resolve pass that follows re-derives the outcome from the repaired arrays
 }
 
 // Element blob offsets: offsets[j] = header_pos(j) - 4*j for the elements whose header lies in
@@ -1092,6 +1162,66 @@ k_des_gather(const uint8_t* __restrict__ stream, const long long* __restrict__ o
     move_tile32<false, WORD_OK>(s_off, s_st, nE, b0, e0, stream, blob, blob_capacity, s_tab, slot, s_queue, &s_qn);
   else
     move_tile<false, WORD_OK>(s_off, nE, b0, e0, stream, blob, blob_capacity, s_tab, slot);
+}
+
+// Gather for long elements. k_des_gather gives every CTA 1024 ELEMENTS, which is 1 GiB of payload when
+// the elements are 1 MiB each: a handful of CTAs then copy the whole stream. Here the work is cut by
+// BYTES instead: a CTA owns kLongSeg bytes of the compact payload, finds the first element that
+// reaches into its segment with a 32-way search over the offsets, and copies element piece by
+// element piece (16 aligned destination bytes per thread and step, source words are 4-byte aligned
+// because an element's payload moves by 4 * (index + 1) bytes). Used when the mean element is >= 2 KiB.
+constexpr int kLongSeg = 32768;
+
+template <bool WORD_OK>
+__global__ void __launch_bounds__(256)
+k_des_gather_long(const uint8_t* __restrict__ stream, const long long* __restrict__ offsets,
+                  const unsigned long long* __restrict__ hdr, uint8_t* __restrict__ blob,
+                  unsigned long long blob_capacity) {
+  __shared__ unsigned long long s_first;
+  if (hdr[DW_STATUS] != 0) return;
+  const unsigned long long N = hdr[DW_NELEM];
+  const unsigned long long total = min((unsigned long long)offsets[N], blob_capacity);
+  const unsigned long long s0 = (unsigned long long)blockIdx.x * kLongSeg;
+  if (s0 >= total) return;
+  const unsigned long long s1 = min(s0 + kLongSeg, total);
+  if (threadIdx.x < 32) {  // largest e with offsets[e] <= s0: 32-way search
+    unsigned long long lo = 0, hi = N;  // answer in [lo, hi)
+    while (hi - lo > 1) {
+      const unsigned long long step = (hi - lo + 31) / 32;
+      const unsigned long long probe = lo + step * (threadIdx.x + 1);
+      const bool le = probe < hi && (unsigned long long)offsets[probe] <= s0;
+      const unsigned m = __ballot_sync(0xffffffffu, le);
+      const int c = __popc(m);  // probes are monotone: the first c lanes are <=
+      const unsigned long long nlo = lo + step * c;
+      hi = min(hi, lo + step * (c + 1));
+      lo = nlo;
+    }
+    if (threadIdx.x == 0) s_first = lo;
+  }
+  __syncthreads();
+  for (unsigned long long e = s_first; e < N; e++) {
+    const unsigned long long o0 = (unsigned long long)offsets[e];
+    if (o0 >= s1) break;
+    const unsigned long long o1 = (unsigned long long)offsets[e + 1];
+    const unsigned long long a = max(o0, s0), b = min(o1, s1);
+    if (a >= b) continue;
+    uint8_t* d = blob + a;
+    const uint8_t* sp = stream + a + 4ull * (e + 1);
+    const unsigned long long n = b - a;
+    const unsigned long long head = min(n, (unsigned long long)((16 - (reinterpret_cast<uintptr_t>(d) & 15)) & 15));
+    if (threadIdx.x < head) d[threadIdx.x] = sp[threadIdx.x];
+    const unsigned long long chunks = (n - head) >> 4;
+    uint8_t* db = d + head;
+    const uint8_t* sb = sp + head;
+    for (unsigned long long c = threadIdx.x; c < chunks; c += 256) {
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) w[k] = load_word(sb + 16 * c + 4 * k, WORD_OK);
+      st_v4(db + 16 * c, w[0], w[1], w[2], w[3]);
+    }
+    const unsigned long long done = head + (chunks << 4);
+    if (done + threadIdx.x < n) d[done + threadIdx.x] = sp[done + threadIdx.x];
+  }
 }
 
 static uint64_t des_chunks(uint64_t stream_bytes) { return (stream_bytes + kDesChunk - 1) / kDesChunk; }
@@ -1224,11 +1354,36 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
   A.err = reinterpret_cast<unsigned int*>(p); p += round_up(K1 * 4, 256);
   A.list = reinterpret_cast<unsigned short*>(p);
   const uint8_t* st = static_cast<const uint8_t*>(stream_dev);
+  // TCB_TIMING=1: per-phase device times on stderr (development aid; adds event records only)
+  static const bool timing = getenv("TCB_TIMING") != nullptr;
+  std::vector<std::pair<const char*, cudaEvent_t>> marks;
+  auto mark = [&](const char* name) {
+    if (!timing) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, s);
+    marks.emplace_back(name, e);
+  };
+  auto report = [&]() {
+    if (!timing || marks.size() < 2) return;
+    cudaEventSynchronize(marks.back().second);
+    for (size_t i = 1; i < marks.size(); i++) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, marks[i - 1].second, marks[i].second);
+      fprintf(stderr, "[tcb] deserialize %-10s %.3f ms\n", marks[i].first, ms);
+    }
+    for (auto& m : marks) cudaEventDestroy(m.second);
+  };
+  mark("start");
   TCB_CUDA(cudaMemsetAsync(hdr, 0, 256, s));
   {
     const unsigned int bias = (unsigned int)(reinterpret_cast<uintptr_t>(st) & 3);
-    const unsigned long long warps = (K + 31) / 32;
-    k_des_speculate<<<(unsigned)((warps + kDesWarps - 1) / kDesWarps), kDesThreads, 0, s>>>(st - bias, bias, stream_bytes, K, A);
+    mark("setup");
+    k_des_vote<<<(unsigned)((K + kVoteWarps - 1) / kVoteWarps), kVoteWarps * 32, 0, s>>>(st - bias, bias, stream_bytes, K, A);
+    mark("vote");
+    k_des_chase<<<(unsigned)((K + kDesThreads - 1) / kDesThreads), kDesThreads, 0, s>>>(st - bias, bias, stream_bytes, K, A, 0);
+    mark("chase");
+    count_launch(1);
   }
   auto resolve = [&]() -> cudaError_t {
     // first mismatch / first error start at ~0 (atomicMin), the scan workspace at 0
@@ -1242,13 +1397,31 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
     return cudaGetLastError();
   };
   TCB_CUDA(resolve());
+  mark("resolve");
   count_launch(1);
   unsigned long long h[DW_HEADER_WORDS];
   TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
   TCB_CUDA(cudaStreamSynchronize(s));
-  if (h[DW_STATUS] == 1) {  // a guess was wrong: repair sequentially, then resolve again
-    k_des_sweep<<<1, 32, 0, s>>>(st, stream_bytes, K, max_elements, A, hdr);
+  // a guess was wrong (elements longer than the 512-byte window, payloads that look like headers):
+  // vote again with a wider window on the chunks that do not fit their predecessor, then whatever is
+  // still inconsistent is repaired by the sequential sweep
+  // (a third round with a 128 KiB window was measured: 20 ms per 256 MiB, slower than the sweep it saves)
+  static const unsigned long long kWide[] = {8ull << 10};
+  for (int r = 0; r < 1 && h[DW_STATUS] == 1; r++) {
+    const unsigned int bias = (unsigned int)(reinterpret_cast<uintptr_t>(st) & 3);
+    k_des_vote_wide<<<(unsigned)((K + kVoteWarps - 1) / kVoteWarps), kVoteWarps * 32, 0, s>>>(st - bias, bias, stream_bytes, K, A, hdr, kWide[r]);
+    k_des_chase<<<(unsigned)((K + kDesThreads - 1) / kDesThreads), kDesThreads, 0, s>>>(st - bias, bias, stream_bytes, K, A, 1);
+    mark("wide vote");
     TCB_CUDA(resolve());
+    count_launch(2);
+    TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
+    TCB_CUDA(cudaStreamSynchronize(s));
+  }
+  if (h[DW_STATUS] == 1) {
+    k_des_sweep<<<1, 32, 0, s>>>(st, stream_bytes, K, max_elements, A, hdr);
+    mark("sweep");
+    TCB_CUDA(resolve());
+    mark("resolve2");
     count_launch(1);
     TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
     TCB_CUDA(cudaStreamSynchronize(s));
@@ -1269,7 +1442,9 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
     TCB_CUDA(cudaStreamSynchronize(s));
     return TCB_OK;
   }
+  mark("host");
   k_des_offsets<<<(unsigned)h[DW_KEND], 64, 0, s>>>(st, stream_bytes, A, hdr, reinterpret_cast<long long*>(offsets_dev));
+  mark("offsets");
   count_launch();
   long long total = 0;
   TCB_CUDA(cudaMemcpyAsync(&total, offsets_dev + N, 8, cudaMemcpyDeviceToHost, s));
@@ -1283,14 +1458,22 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
     uint8_t* blob = static_cast<uint8_t*>(payload_dev);
     const unsigned tiles = (unsigned)((N + kGatTile - 1) / kGatTile);
     const bool word_ok = ((reinterpret_cast<uintptr_t>(st) ^ reinterpret_cast<uintptr_t>(blob)) & 3) == 0;
-    if (word_ok)
+    if ((uint64_t)total / N >= 2048) {  // long elements: cut the work by bytes, not by elements
+      const unsigned segs = (unsigned)(((uint64_t)total + kLongSeg - 1) / kLongSeg);
+      if (word_ok)
+        k_des_gather_long<true><<<segs, 256, 0, s>>>(st, reinterpret_cast<long long*>(offsets_dev), hdr, blob, payload_capacity);
+      else
+        k_des_gather_long<false><<<segs, 256, 0, s>>>(st, reinterpret_cast<long long*>(offsets_dev), hdr, blob, payload_capacity);
+    } else if (word_ok)
       k_des_gather<true><<<tiles, kGatThreads, 0, s>>>(st, reinterpret_cast<long long*>(offsets_dev), hdr, blob, payload_capacity);
     else
       k_des_gather<false><<<tiles, kGatThreads, 0, s>>>(st, reinterpret_cast<long long*>(offsets_dev), hdr, blob, payload_capacity);
     count_launch();
   }
+  mark("gather");
   TCB_CUDA(cudaGetLastError());
   TCB_CUDA(cudaStreamSynchronize(s));
+  report();
   return TCB_OK;
 }
 
