@@ -225,6 +225,24 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
                         uint64_t workspace_bytes, uint64_t* n_elements_host,
                         uint64_t* payload_bytes_host, void* stream);
 
+/* The same decode in two calls, for callers that want to size their buffers exactly (the combined
+ * call needs offsets for the worst case of stream_bytes / 4 elements - 4 GB for a 2 GB stream).
+ * Both replace the same reference loop as TcbBytesDeserialize (utils/__init__.py:249-276).
+ *   Count: chunked offset chase + verification only. *n_elements_host = elements that will be decoded,
+ *          *payload_bound_host = stream_bytes - 4 * n (an upper bound of the payload bytes, exact when
+ *          the whole buffer is decoded). Returns TCB_ERR_TRUNCATED like the combined call.
+ *   Fill : writes offsets (n + 1 entries) and the payload. Must follow a successful Count on the SAME
+ *          workspace, stream_dev, stream_bytes and max_elements, with nothing else having used the
+ *          workspace in between. Both calls synchronise the stream. */
+int TcbBytesDeserializeCount(int device_id, const void* stream_dev, uint64_t stream_bytes,
+                             int64_t max_elements, void* workspace_dev, uint64_t workspace_bytes,
+                             uint64_t* n_elements_host, uint64_t* payload_bound_host, void* stream);
+int TcbBytesDeserializeFill(int device_id, const void* stream_dev, uint64_t stream_bytes,
+                            int64_t max_elements, int64_t* offsets_dev, uint64_t offsets_capacity,
+                            void* payload_dev, uint64_t payload_capacity, void* workspace_dev,
+                            uint64_t workspace_bytes, uint64_t* n_elements_host,
+                            uint64_t* payload_bytes_host, void* stream);
+
 /* =============================================================================================
  * BF16 tensors.
  * Replaces tritonclient/utils/__init__.py:279-323 serialize_bf16_tensor (np.nditer +

@@ -35,7 +35,7 @@ EXPORTS = [
     "TcbPreprocessPlanDestroy", "TcbResampleCoeffs",
     "TcbBytesSerializeWorkspace", "TcbBytesDeserializeWorkspace", "TcbBytesSerialize",
     "TcbBytesSerializeFixedWidth", "TcbBytesDeserialize", "TcbBytesSerializeNoAlloc",
-    "TcbBf16Serialize", "TcbBf16Deserialize",
+    "TcbBf16Serialize", "TcbBf16Deserialize", "TcbBytesDeserializeCount", "TcbBytesDeserializeFill",
 ]
 
 
@@ -108,6 +108,11 @@ _sig("TcbBytesSerializeFixedWidth", c_int,
      [c_int, c_void_p, c_uint32, c_uint64, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p,
       POINTER(c_uint64), c_void_p])
 _sig("TcbBytesDeserialize", c_int,
+     [c_int, c_void_p, c_uint64, c_int64, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p,
+      c_uint64, POINTER(c_uint64), POINTER(c_uint64), c_void_p])
+_sig("TcbBytesDeserializeCount", c_int,
+     [c_int, c_void_p, c_uint64, c_int64, c_void_p, c_uint64, POINTER(c_uint64), POINTER(c_uint64), c_void_p])
+_sig("TcbBytesDeserializeFill", c_int,
      [c_int, c_void_p, c_uint64, c_int64, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p,
       c_uint64, POINTER(c_uint64), POINTER(c_uint64), c_void_p])
 _sig("TcbBf16Serialize", c_int, [c_int, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p])

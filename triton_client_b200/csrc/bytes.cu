@@ -1313,18 +1313,23 @@ int TcbBytesSerializeFixedWidth(int device_id, const void* rows_dev, uint32_t wi
                           workspace_dev, workspace_bytes, total_dev, total_host, stream);
 }
 
-int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_bytes,
-                        int64_t max_elements, int64_t* offsets_dev, uint64_t offsets_capacity,
-                        void* payload_dev, uint64_t payload_capacity, void* workspace_dev,
-                        uint64_t workspace_bytes, uint64_t* n_elements_host,
-                        uint64_t* payload_bytes_host, void* stream) {
+// mode 0: the whole call; 1: count only (everything up to the verified element count); 2: fill only
+// (offsets + gather, on a workspace that a mode-1 call with the same stream left behind)
+enum : int { DES_ALL = 0, DES_COUNT = 1, DES_FILL = 2 };
+
+static int des_impl(int mode, int device_id, const void* stream_dev, uint64_t stream_bytes,
+                    int64_t max_elements, int64_t* offsets_dev, uint64_t offsets_capacity,
+                    void* payload_dev, uint64_t payload_capacity, void* workspace_dev,
+                    uint64_t workspace_bytes, uint64_t* n_elements_host,
+                    uint64_t* payload_bytes_host, void* stream) {
   TCB_CHECK_ARG(n_elements_host != nullptr, "TcbBytesDeserialize: n_elements_host is NULL");
   *n_elements_host = 0;
   if (payload_bytes_host) *payload_bytes_host = 0;
   TCB_DEVICE_GUARD(device_id);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  TCB_CHECK_ARG(offsets_dev != nullptr, "TcbBytesDeserialize: offsets is NULL");
+  TCB_CHECK_ARG(mode == DES_COUNT || offsets_dev != nullptr, "TcbBytesDeserialize: offsets is NULL");
   if (max_elements == 0 || (stream_bytes == 0 && max_elements < 0)) {
+    if (mode == DES_COUNT) return TCB_OK;
     TCB_CUDA(cudaMemsetAsync(offsets_dev, 0, 8, s));
     TCB_CUDA(cudaStreamSynchronize(s));
     return TCB_OK;
@@ -1375,6 +1380,11 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
     for (auto& m : marks) cudaEventDestroy(m.second);
   };
   mark("start");
+  unsigned long long h[DW_HEADER_WORDS];
+  if (mode == DES_FILL) {  // the verified header of the preceding count call
+    TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
+    TCB_CUDA(cudaStreamSynchronize(s));
+  } else {
   TCB_CUDA(cudaMemsetAsync(hdr, 0, 256, s));
   {
     const unsigned int bias = (unsigned int)(reinterpret_cast<uintptr_t>(st) & 3);
@@ -1399,7 +1409,6 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
   TCB_CUDA(resolve());
   mark("resolve");
   count_launch(1);
-  unsigned long long h[DW_HEADER_WORDS];
   TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
   TCB_CUDA(cudaStreamSynchronize(s));
   // a guess was wrong (elements longer than the 512-byte window, payloads that look like headers):
@@ -1426,6 +1435,7 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
     TCB_CUDA(cudaMemcpyAsync(h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
     TCB_CUDA(cudaStreamSynchronize(s));
   }
+  }  // mode != DES_FILL
   if (h[DW_STATUS] == 2)
     return set_error(TCB_ERR_TRUNCATED, "TcbBytesDeserialize: buffer ends inside an element after %llu elements",
                      (unsigned long long)h[DW_NELEM]);
@@ -1433,6 +1443,14 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
     return set_error(TCB_ERR_INTERNAL, "TcbBytesDeserialize: chunk chain did not resolve (status %llu)",
                      (unsigned long long)h[DW_STATUS]);
   const uint64_t N = h[DW_NELEM];
+  if (mode == DES_COUNT) {
+    *n_elements_host = N;
+    // every decoded element spends 4 bytes of the stream on its prefix: an upper bound (exact when the
+    // whole buffer is decoded) of the payload, for the caller to size its buffers with
+    if (payload_bytes_host) *payload_bytes_host = stream_bytes >= 4 * N ? stream_bytes - 4 * N : 0;
+    report();
+    return TCB_OK;
+  }
   if (N > offsets_capacity)
     return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesDeserialize: %llu elements exceed offsets capacity %llu",
                      (unsigned long long)N, (unsigned long long)offsets_capacity);
@@ -1475,6 +1493,33 @@ int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_b
   TCB_CUDA(cudaStreamSynchronize(s));
   report();
   return TCB_OK;
+}
+
+int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_bytes,
+                        int64_t max_elements, int64_t* offsets_dev, uint64_t offsets_capacity,
+                        void* payload_dev, uint64_t payload_capacity, void* workspace_dev,
+                        uint64_t workspace_bytes, uint64_t* n_elements_host,
+                        uint64_t* payload_bytes_host, void* stream) {
+  return des_impl(DES_ALL, device_id, stream_dev, stream_bytes, max_elements, offsets_dev, offsets_capacity,
+                  payload_dev, payload_capacity, workspace_dev, workspace_bytes, n_elements_host,
+                  payload_bytes_host, stream);
+}
+
+int TcbBytesDeserializeCount(int device_id, const void* stream_dev, uint64_t stream_bytes,
+                             int64_t max_elements, void* workspace_dev, uint64_t workspace_bytes,
+                             uint64_t* n_elements_host, uint64_t* payload_bound_host, void* stream) {
+  return des_impl(DES_COUNT, device_id, stream_dev, stream_bytes, max_elements, nullptr, 0, nullptr, 0,
+                  workspace_dev, workspace_bytes, n_elements_host, payload_bound_host, stream);
+}
+
+int TcbBytesDeserializeFill(int device_id, const void* stream_dev, uint64_t stream_bytes,
+                            int64_t max_elements, int64_t* offsets_dev, uint64_t offsets_capacity,
+                            void* payload_dev, uint64_t payload_capacity, void* workspace_dev,
+                            uint64_t workspace_bytes, uint64_t* n_elements_host,
+                            uint64_t* payload_bytes_host, void* stream) {
+  return des_impl(DES_FILL, device_id, stream_dev, stream_bytes, max_elements, offsets_dev, offsets_capacity,
+                  payload_dev, payload_capacity, workspace_dev, workspace_bytes, n_elements_host,
+                  payload_bytes_host, stream);
 }
 
 }  // extern "C"

@@ -127,21 +127,27 @@ def deserialize_from_device(stream, nbytes=None, max_elements=-1, stream_offset=
     nbytes = cap if nbytes is None else int(nbytes)
     if nbytes > cap:
         raise ValueError("stream of %d bytes exceeds the buffer (%d)" % (nbytes, cap))
-    if max_elements is not None and max_elements >= 0:
-        ocap = min(int(max_elements), nbytes // 4)
-    else:
+    if max_elements is None or max_elements < 0:
         max_elements = -1
-        ocap = nbytes // 4
-    offsets = torch.empty(ocap + 1, dtype=torch.int64, device="cuda:%d" % dev)
-    payload = torch.empty(max(nbytes, 1), dtype=torch.uint8, device="cuda:%d" % dev)
+    # count first (chase + verification), then allocate exactly: sizing for the worst case of
+    # nbytes / 4 elements cost 4.2 GB of int64 offsets for a 2.1 GB stream
     ws_bytes = int(_lib.lib.TcbBytesDeserializeWorkspace(nbytes))
     ws = device_buffer(ws_bytes, dev)
     n = _lib.c_uint64(0)
+    bound = _lib.c_uint64(0)
+    s = stream_ptr(dev)
+    rc = _lib.lib.TcbBytesDeserializeCount(dev, src_ptr, nbytes, int(max_elements), ws.data_ptr(), ws_bytes,
+                                           _lib.ctypes.byref(n), _lib.ctypes.byref(bound), s)
+    if rc == _lib.TCB_ERR_TRUNCATED:
+        raise struct.error(_lib.last_error())
+    _lib.check(rc)
+    ocap = int(n.value)
+    offsets = torch.empty(ocap + 1, dtype=torch.int64, device="cuda:%d" % dev)
+    payload = torch.empty(max(int(bound.value), 1), dtype=torch.uint8, device="cuda:%d" % dev)
     pb = _lib.c_uint64(0)
-    rc = _lib.lib.TcbBytesDeserialize(
+    rc = _lib.lib.TcbBytesDeserializeFill(
         dev, src_ptr, nbytes, int(max_elements), offsets.data_ptr(), ocap, payload.data_ptr(),
-        int(payload.numel()), ws.data_ptr(), ws_bytes, _lib.ctypes.byref(n), _lib.ctypes.byref(pb),
-        stream_ptr(dev))
+        int(payload.numel()), ws.data_ptr(), ws_bytes, _lib.ctypes.byref(n), _lib.ctypes.byref(pb), s)
     if rc == _lib.TCB_ERR_TRUNCATED:
         raise struct.error(_lib.last_error())
     _lib.check(rc)
