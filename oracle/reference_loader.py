@@ -42,3 +42,32 @@ def reference_preprocess():
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod.preprocess
+
+
+def reference_http():
+    """The reference's HTTP client module (InferInput, InferRequestedOutput, InferResult,
+    InferenceServerClient.generate_request_body / parse_response_body). Its transport imports are
+    absent from this image, so stand-ins are installed first: ``rapidjson`` -> the standard json
+    module writing compactly (rapidjson's default output has no whitespace), ``gevent`` /
+    ``geventhttpclient`` -> empty modules (never called by the two server-free static methods)."""
+    import json as _json
+
+    reference_utils()
+    if "rapidjson" not in sys.modules:
+        rj = types.ModuleType("rapidjson")
+        rj.dumps = lambda obj, **kw: _json.dumps(obj, separators=(",", ":"))
+        rj.loads = _json.loads
+        sys.modules["rapidjson"] = rj
+    for name in ("gevent", "gevent.pool", "geventhttpclient", "geventhttpclient.url"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    sys.modules["gevent"].pool = sys.modules["gevent.pool"]
+    sys.modules["geventhttpclient"].HTTPClient = object
+    sys.modules["geventhttpclient.url"].URL = object
+    sys.modules["geventhttpclient"].url = sys.modules["geventhttpclient.url"]
+    for name in ("tritonclient.http", "tritonclient.grpc"):  # drop the stubs reference_preprocess() may have left
+        m = sys.modules.get(name)
+        if m is not None and not hasattr(m, "__path__") and not hasattr(m, "InferInput"):
+            del sys.modules[name]
+    import tritonclient.http as h  # noqa
+    return h

@@ -166,3 +166,68 @@ def bf16_cases():
         "fortran": np.asfortranarray(mat),
         "single": np.array([1.5], dtype=np.float32),
     }
+
+
+# ---- HTTP request / response cases -------------------------------------------
+def http_request_cases(h):
+    """name -> thunk returning (inputs, outputs, kwargs) built with the classes of module `h` (the
+    reference's tritonclient.http or triton_client_b200.http). Thunks, because building a BYTES / BF16
+    input serialises it (on the GPU in this repo). Integer JSON data only: rapidjson and json print
+    some floats differently and the reference's rapidjson is a stand-in here."""
+
+    def fixed():
+        a = h.InferInput("INPUT0", [2, 2], "INT32").set_data_from_numpy(np.arange(4, dtype=np.int32).reshape(2, 2))
+        b = h.InferInput("INPUT1", [3], "INT64").set_data_from_numpy(np.array([7, -8, 9], dtype=np.int64), binary_data=False)
+        return [a, b], None, {}
+
+    def text():
+        s = h.InferInput("TEXT", [3], "BYTES").set_data_from_numpy(np.array([b"ab", "he\x00llo", 17], dtype=np.object_))
+        t = h.InferInput("TEXTJ", [2], "BYTES").set_data_from_numpy(np.array([b"x", "yz"], dtype=np.object_), binary_data=False)
+        o = h.InferRequestedOutput("OUT0")
+        oj = h.InferRequestedOutput("OUT1", binary_data=False)
+        oc = h.InferRequestedOutput("CLS", class_count=3)
+        return [s, t], [o, oj, oc], {"request_id": "42"}
+
+    def bf16():
+        rng = np.random.default_rng(5)
+        f = h.InferInput("BF", [2, 3], "BF16").set_data_from_numpy(rng.standard_normal((2, 3)).astype(np.float32))
+        return [f], [h.InferRequestedOutput("OUT0")], {}
+
+    def shm():
+        m = h.InferInput("SHM", [4, 8], "FP32").set_shared_memory("region_a", 128, offset=64)
+        om = h.InferRequestedOutput("OUTSHM")
+        om.set_shared_memory("region_b", 256)
+        return [m], [om], {"sequence_id": 5, "sequence_start": True, "priority": 2, "timeout": 1000,
+                           "parameters": {"foo": "bar", "n": 3}}
+
+    def big():
+        t = h.InferInput("BIGTEXT", [40, 25], "BYTES").set_data_from_numpy(to_object_array(*gbytes(1000)).reshape(40, 25))
+        return [t], None, {"sequence_id": "seq-a", "sequence_end": True}
+
+    def empty():
+        e = h.InferInput("EMPTY", [0], "BYTES").set_data_from_numpy(np.array([], dtype=np.object_))
+        return [e], None, {}
+
+    return {"fixed_binary_and_json_no_outputs": fixed, "bytes_binary_and_json_with_outputs": text, "bf16_binary": bf16,
+            "shared_memory_refs": shm, "gbytes_1000": big, "empty_bytes": empty}
+
+
+def http_response_body():
+    """A response as a server would send it: JSON header + binary sections (FP32, BYTES, BF16, an
+    empty tensor) and one JSON-data output. Returns (body, header_length)."""
+    import json
+    import struct
+
+    fp = np.arange(6, dtype=np.float32).reshape(2, 3)
+    strs = [b"alpha", b"", b"\x00\x01\x02", "résumé".encode()]
+    bytes_sec = b"".join(struct.pack("<I", len(x)) + x for x in strs)
+    bf = (np.array([1.5, -2.0, 3.140625], dtype=np.float32).view(np.uint32) >> 16).astype("<u2").tobytes()
+    hdr = {"model_name": "m", "model_version": "1", "id": "42", "outputs": [
+        {"name": "OUT_FP32", "datatype": "FP32", "shape": [2, 3], "parameters": {"binary_data_size": fp.nbytes}},
+        {"name": "OUT_BYTES", "datatype": "BYTES", "shape": [2, 2], "parameters": {"binary_data_size": len(bytes_sec)}},
+        {"name": "OUT_JSON", "datatype": "INT64", "shape": [3], "data": [1, 2, 3]},
+        {"name": "OUT_BF16", "datatype": "BF16", "shape": [3], "parameters": {"binary_data_size": len(bf)}},
+        {"name": "OUT_EMPTY", "datatype": "INT32", "shape": [0], "parameters": {"binary_data_size": 0}},
+    ]}
+    hj = json.dumps(hdr, separators=(",", ":")).encode()
+    return hj + fp.tobytes() + bytes_sec + bf, len(hj)

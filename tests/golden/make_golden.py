@@ -92,6 +92,29 @@ def main():
                             "back_sha256": sha(np.ascontiguousarray(back).tobytes())})
     with open(os.path.join(HERE, "bf16_golden.json"), "w") as f:
         json.dump(bf, f, indent=1)
+    # ---- HTTP request bodies / response parsing (reference http module behind transport stand-ins) -----
+    import gzip
+
+    h = rl.reference_http()
+    hg = {"env": env, "note": "rapidjson is absent from the image: the reference ran with a stand-in that writes "
+                              "JSON compactly like rapidjson's default", "requests": [], "responses": []}
+    for name, thunk in cases.http_request_cases(h).items():
+        inputs, outputs, kw = thunk()
+        body, json_size = h.InferenceServerClient.generate_request_body(inputs, outputs=outputs, **kw)
+        hg["requests"].append({"name": name, "json_size": json_size, "body_sha256": sha(body), "body_len": len(body),
+                               "header": body[:json_size].decode() if json_size else body.decode()})
+    body, hl = cases.http_response_body()
+    for enc in (None, "gzip"):
+        payload = gzip.compress(body) if enc == "gzip" else body
+        res = h.InferenceServerClient.parse_response_body(payload, header_length=hl, content_encoding=enc)
+        rec = {"encoding": enc, "outputs": []}
+        for out in res.get_response()["outputs"]:
+            arr = res.as_numpy(out["name"])
+            rec["outputs"].append({"name": out["name"], "dtype": str(arr.dtype), "shape": list(arr.shape),
+                                   "items": [x.hex() if isinstance(x, bytes) else repr(x) for x in arr.ravel().tolist()]})
+        hg["responses"].append(rec)
+    with open(os.path.join(HERE, "http_golden.json"), "w") as f:
+        json.dump(hg, f, indent=1)
     print("wrote goldens:", len(gold["cases"]), "preprocess cases,", len(bg["gbytes"]), "gbytes,",
           len(bg["objects"]), "object cases")
 
