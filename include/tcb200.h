@@ -88,6 +88,28 @@ int TcbDeviceFree(int device_id, void* ptr_dev);
 int TcbMemcpy(int device_id, void* dst, const void* src, uint64_t byte_size, void* stream, int sync);
 
 /* =============================================================================================
+ * System (POSIX) shared-memory regions.
+ * Replaces libcshm: tritonclient/utils/shared_memory/shared_memory.cc:76-105 SharedMemoryRegionCreate,
+ * :107-116 SharedMemoryRegionSet, :118-131 GetSharedMemoryHandleInfo, :133-148
+ * SharedMemoryRegionDestroy (declared in shared_memory.h:34-53). Same return codes for the failures
+ * libcshm knows (-2 shm_open, -3 ftruncate, -4 mmap, -5 shm_unlink, -6 munmap).
+ * pin != 0 page-locks the mapping (cudaHostRegister, best effort) so that device <-> region
+ * copies run by DMA; copies are bounds-checked (libcshm's are not).
+ * ============================================================================================= */
+int TcbShmRegionCreate(const char* triton_shm_name, const char* shm_key, uint64_t byte_size,
+                       int pin, void** shm_handle);
+int TcbShmRegionSet(void* shm_handle, uint64_t offset, uint64_t byte_size, const void* data);
+/* Any out pointer may be NULL. offset is always 0 (libcshm maps the whole object too). */
+int TcbShmRegionInfo(void* shm_handle, void** shm_addr, const char** shm_key, int* shm_fd,
+                     uint64_t* offset, uint64_t* byte_size, int* pinned);
+/* Copy byte_size bytes between device memory and region + offset on `stream` (to_region != 0:
+ * device -> region), then synchronise the stream. No counterpart in libcshm: the reference moves
+ * device results to a system region through a numpy array. */
+int TcbShmRegionCopyDevice(void* shm_handle, uint64_t offset, void* dev_ptr, uint64_t byte_size,
+                           int device_id, int to_region, void* stream);
+int TcbShmRegionDestroy(void* shm_handle);
+
+/* =============================================================================================
  * Image preprocess.
  * Replaces image_client.py:154-193 `preprocess` (PIL convert + resize(BILINEAR) + numpy
  * astype/scale/transpose, /root/reference/src/python/examples/image_client.py) and the

@@ -36,6 +36,7 @@ EXPORTS = [
     "TcbBytesSerializeWorkspace", "TcbBytesDeserializeWorkspace", "TcbBytesSerialize",
     "TcbBytesSerializeFixedWidth", "TcbBytesDeserialize", "TcbBytesSerializeNoAlloc",
     "TcbBf16Serialize", "TcbBf16Deserialize", "TcbBytesDeserializeCount", "TcbBytesDeserializeFill",
+    "TcbShmRegionCreate", "TcbShmRegionSet", "TcbShmRegionInfo", "TcbShmRegionCopyDevice", "TcbShmRegionDestroy",
 ]
 
 
@@ -110,6 +111,12 @@ _sig("TcbBytesSerializeFixedWidth", c_int,
 _sig("TcbBytesDeserialize", c_int,
      [c_int, c_void_p, c_uint64, c_int64, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p,
       c_uint64, POINTER(c_uint64), POINTER(c_uint64), c_void_p])
+_sig("TcbShmRegionCreate", c_int, [c_char_p, c_char_p, c_uint64, c_int, POINTER(c_void_p)])
+_sig("TcbShmRegionSet", c_int, [c_void_p, c_uint64, c_uint64, c_void_p])
+_sig("TcbShmRegionInfo", c_int, [c_void_p, POINTER(c_void_p), POINTER(c_char_p), POINTER(c_int), POINTER(c_uint64),
+                                 POINTER(c_uint64), POINTER(c_int)])
+_sig("TcbShmRegionCopyDevice", c_int, [c_void_p, c_uint64, c_void_p, c_uint64, c_int, c_int, c_void_p])
+_sig("TcbShmRegionDestroy", c_int, [c_void_p])
 _sig("TcbBytesDeserializeCount", c_int,
      [c_int, c_void_p, c_uint64, c_int64, c_void_p, c_uint64, POINTER(c_uint64), POINTER(c_uint64), c_void_p])
 _sig("TcbBytesDeserializeFill", c_int,
