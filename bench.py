@@ -937,7 +937,7 @@ def main():
             t_pg = cx.max_over_ranks(time.perf_counter() - t0)
             pg_ok = cx.sum_over_ranks(1.0 if np.array_equal(out_np, ref_out.numpy()) else 0.0) == world
             pageable = {"value": world * n * reps / t_pg, "unit": "images/s", "matches_device_run": pg_ok,
-                        "path": "HostBatchPipeline.run_pageable: numpy array -> CPU copy into two pinned staging buffers -> "
+                        "path": "HostBatchPipeline.run_pageable: numpy array -> the library's pinned staging ring (parallel host copy) -> "
                                 "H2D | kernel | D2H -> numpy array (wall clock, %d passes)" % reps}
             del src_np, out_np
         except Exception as ex:
