@@ -153,6 +153,37 @@ __device__ __forceinline__ void store_elem(uint8_t* __restrict__ dst, size_t idx
   if (ELEM == 8) reinterpret_cast<uint64_t*>(dst)[idx] = *reinterpret_cast<const uint64_t*>(lut_entry);
 }
 
+// ---- same-size images (no resample pass at all): value table + layout only, four pixels per thread ----
+template <int ELEM> struct ElemOf;
+template <> struct ElemOf<1> { using type = uint8_t; };
+template <> struct ElemOf<2> { using type = uint16_t; };
+template <> struct ElemOf<4> { using type = uint32_t; };
+template <> struct ElemOf<8> { using type = unsigned long long; };
+
+// RUN (multiple of 4) consecutive elements v[first..] to a destination aligned to min(16, 4 * ELEM) bytes
+template <int ELEM, int RUN, int N>
+__device__ __forceinline__ void store_run(uint8_t* __restrict__ p, const typename ElemOf<ELEM>::type (&v)[N], int first) {
+#pragma unroll
+  for (int k = 0; k < RUN; k += 4) {
+    if (ELEM == 1) {
+      *reinterpret_cast<uint32_t*>(p + k) = (uint32_t)v[first + k] | ((uint32_t)v[first + k + 1] << 8) |
+                                            ((uint32_t)v[first + k + 2] << 16) | ((uint32_t)v[first + k + 3] << 24);
+    } else if (ELEM == 2) {
+      *reinterpret_cast<uint2*>(p + 2 * k) = make_uint2((uint32_t)v[first + k] | ((uint32_t)v[first + k + 1] << 16),
+                                                        (uint32_t)v[first + k + 2] | ((uint32_t)v[first + k + 3] << 16));
+    } else if (ELEM == 4) {
+      *reinterpret_cast<uint4*>(p + 4 * k) = make_uint4((uint32_t)v[first + k], (uint32_t)v[first + k + 1],
+                                                        (uint32_t)v[first + k + 2], (uint32_t)v[first + k + 3]);
+    } else {
+#pragma unroll
+      for (int h = 0; h < 4; h += 2) {
+        const unsigned long long a = (unsigned long long)v[first + k + h], b = (unsigned long long)v[first + k + h + 1];
+        *reinterpret_cast<uint4*>(p + 8 * (k + h)) = make_uint4((uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+      }
+    }
+  }
+}
+
 // Pass 2: second pass (or the only pass, or none) + value table + layout, one thread per output
 // pixel.
 template <int C, int ELEM>
@@ -174,6 +205,38 @@ k_resample_pass2(const ImgDesc* __restrict__ descs, const int32_t* __restrict__ 
     in = d.src; in_pitch = d.pitch; in_cin = d.cin;
   }
   uint8_t* o = dst + (size_t)img * C * out_h * out_w * ELEM;
+  if (d.p2_axis == AXIS_NONE && (out_w & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+    // nothing to resample in this pass: four consecutive pixels per thread, vector stores
+    using E = typename ElemOf<ELEM>::type;
+    const E* __restrict__ tab = reinterpret_cast<const E*>(lut);
+    const int g0 = (blockIdx.x - blk[img]) * (kTwoPassThreads * kPass2Px / 4) + threadIdx.x;
+    const size_t plane = (size_t)out_h * out_w;
+#pragma unroll
+    for (int r = 0; r < kPass2Px / 4; r++) {
+      const int local = 4 * (g0 + r * kTwoPassThreads);
+      if (local >= out_h * out_w) return;
+      const int y = local / out_w, x = local - y * out_w;
+      const uint8_t* row = in + (size_t)y * in_pitch;
+      E vals[4 * C];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        int u[C];
+        fetch_px<C>(row, in_cin, x + j, u);
+#pragma unroll
+        for (int ch = 0; ch < C; ch++) {
+          const E e = __ldg(tab + ch * 256 + u[ch]);
+          if (layout == TCB_LAYOUT_NCHW) vals[ch * 4 + j] = e; else vals[j * C + ch] = e;
+        }
+      }
+      if (layout == TCB_LAYOUT_NCHW) {
+#pragma unroll
+        for (int ch = 0; ch < C; ch++) store_run<ELEM, 4>(o + ((size_t)ch * plane + local) * ELEM, vals, ch * 4);
+      } else {
+        store_run<ELEM, 4 * C>(o + (size_t)local * C * ELEM, vals, 0);
+      }
+    }
+    return;
+  }
   const int local0 = (blockIdx.x - blk[img]) * (kTwoPassThreads * kPass2Px) + threadIdx.x;
   for (int px = 0; px < kPass2Px; px++) {  // consecutive threads take consecutive pixels in every round
   const int local = local0 + px * kTwoPassThreads;

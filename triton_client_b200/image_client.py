@@ -59,6 +59,9 @@ class PreprocessPlan:
             pitch = int(s[3]) if len(s) > 3 else wd * ch
             self.images[i] = _lib.TcbImage(0, wd, ht, pitch, ch)
         self.sizes = [(im.width, im.height, im.src_channels, im.pitch) for im in self.images]
+        # the src_dev fields of the descriptor array, as one strided numpy view
+        self._src = np.ndarray((self.n,), dtype=np.uint64, buffer=self.images, offset=0,
+                               strides=(ctypes.sizeof(_lib.TcbImage),)) if self.n else np.zeros(0, np.uint64)
         self._plan = ctypes.c_void_p()
         self._path = path
         self._created = False
@@ -71,8 +74,19 @@ class PreprocessPlan:
         return (self.n, self.h, self.w, self.c)
 
     def _ensure(self, ptrs):
-        for i, p in enumerate(ptrs):
-            self.images[i].src_dev = int(p)
+        """Stores the source addresses. Returns the descriptor array for TcbPreprocessPlanRun, or None when
+        nothing changed since the previous run (the plan then skips validation and the descriptor upload:
+        with thousands of images per batch that is most of the host time of a call)."""
+        if ptrs is not None:
+            if isinstance(ptrs, np.ndarray) and ptrs.dtype == np.uint64 and ptrs.shape == (self.n,):
+                new = ptrs  # callers with thousands of images keep their addresses in an array
+            else:
+                new = np.fromiter((int(p) for p in ptrs), dtype=np.uint64, count=self.n)
+            if self._created and np.array_equal(new, self._src):
+                return None
+            self._src[:] = new
+        elif self._created:
+            return None
         if not self._created:
             # created lazily with real pointers: the fused kernel's eligibility depends on alignment
             _lib.check(_lib.lib.TcbPreprocessPlanCreate(
