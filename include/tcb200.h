@@ -285,6 +285,20 @@ int TcbBf16Serialize(int device_id, const void* src_f32_dev, uint64_t n_elements
 int TcbBf16Deserialize(int device_id, const void* src_dev, uint64_t src_bytes, void* dst_f32_dev,
                        uint64_t dst_capacity, void* stream);
 
+/* =============================================================================================
+ * Classification strings: field split on the device (postprocess half)
+ * Replaces the per-character join and ':' split of every element in
+ *   /root/reference/src/python/examples/image_client.py:196-216 (postprocess)
+ * for outputs decoded by TcbBytesDeserialize(Fill): payload_dev + offsets_dev (num_elements + 1
+ * int64, as written by the deserialiser). fields_dev receives 4 int64 per element: the positions,
+ * relative to the element's first byte, of its first, second and third ':' (-1 where it has fewer),
+ * and the element's length. The caller slices cls[0] = [0, f0), cls[1] = (f0, f1), cls[2] =
+ * (f1, f2 or end) - what str.split(":")[0:3] yields; an element with f1 == -1 makes the reference
+ * raise IndexError.
+ * ============================================================================================= */
+int TcbClassificationFields(int device_id, const void* payload_dev, const int64_t* offsets_dev,
+                            int64_t num_elements, int64_t* fields_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -38,10 +38,20 @@ def reference_preprocess():
         mi = types.SimpleNamespace(FORMAT_NONE=0, FORMAT_NHWC=1, FORMAT_NCHW=2)
         mc.ModelInput = mi
     sys.modules["tritonclient.grpc"].model_config_pb2 = mc
+    return _image_client_module().preprocess
+
+
+def _image_client_module():
     spec = importlib.util.spec_from_file_location("_ref_image_client", _IMAGE_CLIENT)
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
-    return mod.preprocess
+    return mod
+
+
+def reference_postprocess():
+    """The reference example's postprocess(results, output_name, batch_size, supports_batching)."""
+    reference_preprocess()  # installs the transport stand-ins
+    return _image_client_module().postprocess
 
 
 def reference_http():

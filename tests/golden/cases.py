@@ -231,3 +231,41 @@ def http_response_body():
     ]}
     hj = json.dumps(hdr, separators=(",", ":")).encode()
     return hj + fp.tobytes() + bytes_sec + bf, len(hj)
+
+
+def postprocess_cases():
+    """Classification outputs as a server's classification extension sends them
+    ("score:index:label" per element): name -> (object array, batch_size, supports_batching).
+    A case whose value list ends with an element of fewer than three fields raises in the
+    reference after the lines before it were printed."""
+    def arr(rows):
+        a = np.empty((len(rows), len(rows[0])), dtype=np.object_)
+        for i, r in enumerate(rows):
+            for j, x in enumerate(r):
+                a[i, j] = x
+        return a
+
+    def arr1(items):
+        a = np.empty(len(items), dtype=np.object_)
+        for i, x in enumerate(items):
+            a[i] = x
+        return a
+
+    rng = np.random.default_rng(77)
+    big = [[("%.6f:%d:label %d/%d" % (rng.random(), rng.integers(0, 1000), i, j)).encode() for j in range(5)]
+           for i in range(64)]
+    long_label = b"0.5:3:" + bytes(rng.integers(32, 127, 300, dtype=np.uint8).tolist()).replace(b":", b";")
+    return {
+        "batch2_top3": (arr([[b"0.87:281:tabby cat", b"0.09:282:tiger cat", b"0.01:285:Egyptian cat"],
+                             [b"0.5:1:goldfish", b"0.25:2:shark", b"0.125:3:ray"]]), 2, True),
+        "non_batching_top2": (arr1([b"12.5:7:cock", b"11.0:8:hen"]), 1, False),
+        "label_with_colons": (arr([[b"0.1:7:a:b:c", b"1:2:3:"]]), 1, True),
+        "empty_fields": (arr([[b"::", b":5:", b"x::y"]]), 1, True),
+        "latin1_bytes": (arr([[b"\xe9:1:caf\xe9", bytes(range(128, 140)) + b":0:" + bytes(range(250, 256))]]), 1, True),
+        "colon_at_word_edges": (arr([[b"0123456789abcdef0123456789abcde:1:2", b"0123456789abcdef0123456789abcdef:1:2",
+                                      b"a" * 63 + b":" + b"b" * 32 + b":" + b"c" * 70]]), 1, True),
+        "long_label": (arr([[long_label]]), 1, True),
+        "batch64_top5": (arr(big), 64, True),
+        "too_few_fields_raises": (arr([[b"0.9:1:ok", b"0.1:2"]]), 1, True),
+        "batch_mismatch_raises": (arr([[b"0.9:1:ok"]]), 2, True),
+    }

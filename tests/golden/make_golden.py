@@ -115,6 +115,31 @@ def main():
         hg["responses"].append(rec)
     with open(os.path.join(HERE, "http_golden.json"), "w") as f:
         json.dump(hg, f, indent=1)
+    # ---- classification postprocess (the reference example's own function, stdout captured) -------------
+    import contextlib
+    import io
+
+    post = rl.reference_postprocess()
+
+    class _Result:
+        def __init__(self, a):
+            self.a = a
+
+        def as_numpy(self, name):
+            return self.a
+
+    pg = {"env": env, "cases": []}
+    for name, (a, batch, batching) in cases.postprocess_cases().items():
+        buf, err = io.StringIO(), None
+        try:
+            with contextlib.redirect_stdout(buf):
+                post(_Result(a), "OUT", batch, batching)
+        except Exception as e:  # the reference raises for malformed elements / a wrong row count
+            err = [type(e).__name__, str(e)]
+        text = buf.getvalue()  # split on "\n" only: str.splitlines() also cuts at \x85 and friends
+        pg["cases"].append({"name": name, "lines": text.split("\n")[:-1] if text else [], "raises": err})
+    with open(os.path.join(HERE, "postprocess_golden.json"), "w") as f:
+        json.dump(pg, f, indent=1)
     print("wrote goldens:", len(gold["cases"]), "preprocess cases,", len(bg["gbytes"]), "gbytes,",
           len(bg["objects"]), "object cases")
 

@@ -37,6 +37,7 @@ EXPORTS = [
     "TcbBytesSerializeFixedWidth", "TcbBytesDeserialize", "TcbBytesSerializeNoAlloc",
     "TcbBf16Serialize", "TcbBf16Deserialize", "TcbBytesDeserializeCount", "TcbBytesDeserializeFill",
     "TcbShmRegionCreate", "TcbShmRegionSet", "TcbShmRegionInfo", "TcbShmRegionCopyDevice", "TcbShmRegionDestroy",
+    "TcbClassificationFields",
 ]
 
 
@@ -124,6 +125,7 @@ _sig("TcbBytesDeserializeFill", c_int,
       c_uint64, POINTER(c_uint64), POINTER(c_uint64), c_void_p])
 _sig("TcbBf16Serialize", c_int, [c_int, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p])
 _sig("TcbBf16Deserialize", c_int, [c_int, c_void_p, c_uint64, c_void_p, c_uint64, c_void_p])
+_sig("TcbClassificationFields", c_int, [c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p])
 
 
 def last_error():

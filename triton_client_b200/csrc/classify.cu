@@ -46,8 +46,7 @@ extern "C" int TcbClassificationFields(int device_id, const void* payload_dev, c
   TCB_CHECK_ARG(num_elements >= 0, "TcbClassificationFields: negative element count");
   if (num_elements == 0) return TCB_OK;
   TCB_CHECK_ARG(offsets_dev && fields_dev, "TcbClassificationFields: NULL argument");
-  DeviceGuard guard(device_id);
-  if (!guard.ok()) return guard.rc();
+  TCB_DEVICE_GUARD(device_id);
   const int64_t want = (num_elements + 7) / 8;  // eight warps per CTA
   const int ctas = (int)std::min<int64_t>(want, (int64_t)sm_count(device_id) * 16);
   k_class_fields<<<ctas, 256, 0, static_cast<cudaStream_t>(stream)>>>(

@@ -322,3 +322,88 @@ def preprocess(img, format, dtype, c, h, w, scaling, protocol=None):
     plan.run([d_src.data_ptr()], d_out.data_ptr(), plan.out_bytes_per_image, stream=s)
     host = to_host(d_out.data_ptr(), plan.out_bytes_per_image, dev)  # synchronises
     return host.view(plan.out_dtype).reshape(plan.out_shape[1:])
+
+
+# ---- the step after the decode: classification strings ----------------------
+def classification_fields(offsets, payload, device=None):
+    """First three ':' of every element of a decoded BYTES tensor, on the device.
+
+    offsets [n + 1] int64 / payload uint8 CUDA tensors as returned by
+    ``utils.deserialize_from_device``. Returns an int64 CUDA tensor [n, 4]: positions of the first,
+    second and third ':' relative to the element (-1: fewer), and the element's length."""
+    import torch
+
+    n = int(offsets.numel()) - 1
+    dev = offsets.device.index if device is None else device
+    fields = torch.empty((max(n, 0), 4), dtype=torch.int64, device="cuda:%d" % dev)
+    if n > 0:
+        _lib.check(_lib.lib.TcbClassificationFields(dev, payload.data_ptr(), offsets.data_ptr(), n,
+                                                    fields.data_ptr(), stream_ptr(dev)))
+    return fields
+
+
+def iter_classification_lines(offsets, payload, device=None):
+    """Yields the lines the reference's postprocess() prints for these elements, in element order:
+    ``"    {score} ({index}) = {label}"`` with the three fields cut at the element's first three
+    ':' and every byte taken as one character (image_client.py:211-216 of the reference joins
+    ``chr(x)`` per byte, i.e. Latin-1). An element with fewer than two ':' raises IndexError, as
+    ``cls[2]`` does there."""
+    fields = classification_fields(offsets, payload, device).cpu().numpy()
+    n = fields.shape[0]
+    if n == 0:
+        return
+    offs = offsets.cpu().numpy()
+    raw = payload[:int(offs[n])].cpu().numpy().tobytes() if int(offs[n]) else b""
+    for b, (f0, f1, f2, ln) in zip(offs[:n].tolist(), fields.tolist()):
+        if f1 < 0:
+            raise IndexError("list index out of range")
+        end = ln if f2 < 0 else f2
+        yield "    {} ({}) = {}".format(raw[b:b + f0].decode("latin-1"), raw[b + f0 + 1:b + f1].decode("latin-1"),
+                                        raw[b + f1 + 1:b + end].decode("latin-1"))
+
+
+def classification_lines(offsets, payload, device=None):
+    return list(iter_classification_lines(offsets, payload, device))
+
+
+def _host_classification_lines(output_array, supports_batching):
+    """Outputs that did not come through the BYTES decode (JSON data, str arrays): the reference's
+    own per-element handling (image_client.py:207-216)."""
+    for results in output_array:
+        for result in (results if supports_batching else [results]):
+            text = bytes(result).decode("latin-1") if output_array.dtype.type == np.object_ else result
+            cls = text.split(":")
+            yield "    {} ({}) = {}".format(cls[0], cls[1], cls[2])
+
+
+def _postprocess_iter(results, output_name, batch_size, supports_batching):
+    """BYTES outputs that arrived as binary data are decoded and split on the device
+    (``results.as_device``); anything else goes through ``results.as_numpy`` like the reference."""
+    out = results.get_output(output_name) if hasattr(results, "get_output") else None
+    shape = list(out["shape"]) if isinstance(out, dict) and "shape" in out else None
+    dev = None
+    if (shape is not None and out.get("datatype") == "BYTES" and hasattr(results, "as_device")
+            and 1 <= len(shape) <= (2 if supports_batching else 1)):
+        dev = results.as_device(output_name)
+    if dev is None:
+        output_array = results.as_numpy(output_name)
+        if supports_batching and len(output_array) != batch_size:
+            raise Exception("expected {} results, got {}".format(batch_size, len(output_array)))
+        return _host_classification_lines(output_array, supports_batching)
+    if supports_batching and int(shape[0]) != batch_size:
+        raise Exception("expected {} results, got {}".format(batch_size, int(shape[0])))
+    offsets, payload = dev
+    return iter_classification_lines(offsets, payload)
+
+
+def postprocess_lines(results, output_name, batch_size, supports_batching):
+    """What postprocess() prints, as a list of lines."""
+    return list(_postprocess_iter(results, output_name, batch_size, supports_batching))
+
+
+def postprocess(results, output_name, batch_size, supports_batching):
+    """Post-process results to show classifications: drop-in for
+    /root/reference/src/python/examples/image_client.py:196-216 (same checks, same text, printed
+    element by element so that a malformed element raises after its predecessors were shown)."""
+    for line in _postprocess_iter(results, output_name, batch_size, supports_batching):
+        print(line)
