@@ -222,6 +222,10 @@ int TcbBytesSerialize(int device_id, const void* payload_dev, const void* length
  *     before its kernel runs, so back-to-back calls on one stream are fine; two calls whose GPU
  *     work can overlap (different streams, different threads) race on it and must be ordered by
  *     the caller.
+ *   - Errors found on the device (destination too small: TCB_ERR_CAPACITY) are reported through
+ *     the synchronising form only, i.e. when total_host is given. With total_host == NULL the call
+ *     returns once the work is enqueued and has nowhere to report them (there is no total_dev
+ *     here): size dst_capacity from the lengths (payload bytes + 4 per element) before using it.
  * Arguments as TcbBytesSerialize, minus the workspace and total_dev. */
 int TcbBytesSerializeNoAlloc(int device_id, const void* payload_dev, const void* lengths_dev,
                              int length_size, uint64_t n_elements, void* dst_dev,
