@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(BIG ? 512 : 256, BIG ? 1 : 3)
 k_preprocess_fused(const FusedDesc* __restrict__ descs, const int4* __restrict__ items,
                    const int32_t* __restrict__ cta_first, const int32_t* __restrict__ pool,
                    const uint8_t* __restrict__ lut, uint8_t* __restrict__ dst, int out_h, int out_w,
-                   int layout, int elem, int dst_aligned16) {
+                   int layout, int elem, int flags) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, nthreads = blockDim.x;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -193,7 +193,7 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int4* __restrict__
   const bool fast1 = d.cin == 1 && C == 1;
   const bool rows_al4 = d.aligned4 != 0;
   // vertical pass: units of 4 consecutive output elements; unit -> (line, x4) fixed per thread
-  const bool vec4 = dst_aligned16 && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));
+  const bool vec4 = (flags & 1) && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));  // bit 0: dst is 16-byte aligned
   const int upl = nchw ? out_w / 4 : L / 4;  // units per line (vec4 only)
   const int n_units = vec4 ? (nchw ? C * upl : upl) : 0;
   const int32_t* vg = pool + d.vg_off;
@@ -437,6 +437,14 @@ k_preprocess_fused(const FusedDesc* __restrict__ descs, const int4* __restrict__
       deinterleave(i);
       __syncthreads();  // raw stage drained, P4 complete
       if (tid == 0 && i + 1 < n_groups) issue(i + 1);
+      if ((flags >> 1) && tid == 32 && i + 1 + (flags >> 1) < n_groups) {  // the group after that one: towards L2
+        const int gp = g_first + i + 1 + (flags >> 1);
+        const int r1 = min(4 * gp + 4, d.H);
+        const uintptr_t start = reinterpret_cast<uintptr_t>(d.src) + (size_t)(4 * gp) * d.pitch;
+        const uintptr_t end = reinterpret_cast<uintptr_t>(d.src) + (size_t)(r1 - 1) * d.pitch + (size_t)d.W * d.cin;
+        const uintptr_t a0 = start & ~(uintptr_t)15, a1 = (end + 15) & ~(uintptr_t)15;
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"((uint32_t)(a1 - a0)) : "memory");
+      }
       if (tmp_idx0 >= 0) {
         const uint4* Pb = P4;
         uint32_t* out = tmp4 + (size_t)slot * L + tmp_idx0;
@@ -527,7 +535,7 @@ __global__ void __launch_bounds__(WMAX * 32, WMAX <= 16 ? 2 : 1)
 k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restrict__ items,
                        const int32_t* __restrict__ cta_first, const int32_t* __restrict__ pool,
                        const uint8_t* __restrict__ lut, uint8_t* __restrict__ dst, int out_h, int out_w,
-                       int layout, int elem, int dst_aligned16) {
+                       int layout, int elem, int flags) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int C = 3;
   constexpr int kMmaTilesPerWarp = TPW;
@@ -549,7 +557,7 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
   const int L = out_w * C;
   const int ntiles = (out_w + 7) >> 3;
   // ---- vertical-pass constants (depend on the launch only) ---------------------------------------
-  const bool vec4 = dst_aligned16 && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));
+  const bool vec4 = (flags & 1) && (nchw ? (out_w % 4 == 0) : (L % 4 == 0));  // bit 0: dst is 16-byte aligned
   const int upl = nchw ? out_w / 4 : L / 4;       // units (4 consecutive output elements) per line
   const int n_units = vec4 ? (nchw ? C * upl : upl) : 0;
   const int vb_rows = n_units > 0 ? max(1, nthreads / n_units) : 1;  // output rows handled side by side
@@ -698,6 +706,14 @@ k_preprocess_fused_mma(const FusedDesc* __restrict__ descs, const int4* __restri
       }
       __syncthreads();  // raw drained, P complete
       if (tid == 0 && s + NST <= s_last) issue(s + NST);  // into the stage that has just been drained
+      // flags >> 1: also ask L2 for the rows of the step after that one, so that its bulk copy, issued one
+      // step from now with a single step to land, finds them on chip (cfg3: 0.431 -> 0.426 ms; two or more
+      // steps ahead is slower: 0.427, 0.432, 0.448 ms for 2, 3, 4)
+      if ((flags >> 1) && tid == 32 && s + NST + (flags >> 1) <= s_last) {
+        const int r0 = 8 * (s + NST + (flags >> 1)), r1 = min(r0 + 8, d.H);
+        const uint32_t bytes = (uint32_t)((r1 - r0 - 1) * d.pitch + ((d.W * 3 + 15) & ~15));
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(d.src + (size_t)r0 * d.pitch), "r"(bytes) : "memory");
+      }
       // ---- horizontal pass: IMMA ----------------------------------------------------------------------
       // (tiles beyond the last one compute on all-zero fragments and store nothing: no branch per tile)
       uint32_t* st_ptr = tmp4 + (own_half ? slotB : slotA) * L + st_base;
@@ -1328,7 +1344,8 @@ int fused_update_sources(const Plan& p, cudaStream_t s) {
 int fused_launch(const Plan& p, void* dst, cudaStream_t s) {
   const FusedPlan* fp = fused_of(p);
   if (!fp) return set_error(TCB_ERR_INTERNAL, "fused plan missing");
-  const int al = (reinterpret_cast<uintptr_t>(dst) % 16 == 0) ? 1 : 0;
+  static const int pf = (getenv("TCB_FUSED_L2PF") ? atoi(getenv("TCB_FUSED_L2PF")) : 1) << 1;  // L2 prefetch distance (IMMA kernel)
+  const int al = ((reinterpret_cast<uintptr_t>(dst) % 16 == 0) ? 1 : 0) | pf;
   for (auto& kv : fp->cls) {
     const FusedClass& fc = kv.second;
     const int ctas = (int)fc.cta_first.size() - 1;
