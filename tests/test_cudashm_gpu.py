@@ -164,3 +164,52 @@ def test_large_pageable_copies_go_through_the_staging_ring_and_round_trip(nbytes
         assert np.array_equal(got[0], f) and np.array_equal(got[1], f[::-1])
     finally:
         cudashm.destroy_shared_memory_region(region)
+
+
+def test_large_results_come_in_recycled_page_locked_buffers():
+    """get_contents_as_numpy of a large fixed-dtype tensor: right bytes, a new array every call, the
+    buffer recycled only after the last view of it died (utils/cuda_shared_memory/_host_pool.py)."""
+    import gc
+
+    torch, utils, cudashm = _mods()
+    from triton_client_b200.utils.cuda_shared_memory import _host_pool
+
+    n = 3 * (1 << 20) + 123  # > 2 MiB: pooled
+    src = np.random.default_rng(3).integers(0, 2**31, n, dtype=np.int32)
+    h = cudashm.create_shared_memory_region("pool_data", src.nbytes, 0)
+    cudashm.set_shared_memory_region(h, [src])
+    try:
+        def addr(x):  # not x.ctypes.data inside an assert: pytest's rewritten asserts keep such temporaries alive
+            return x.__array_interface__["data"][0]
+
+        a = cudashm.get_contents_as_numpy(h, np.int32, [n])
+        assert a.dtype == np.int32 and a.shape == (n,) and a.flags.writeable
+        assert np.array_equal(a, src)
+        held = _host_pool.pool_stats()["held_bytes"]
+        assert held >= src.nbytes
+        view = a[1000:2000]
+        a_addr = addr(a)
+        b = cudashm.get_contents_as_numpy(h, np.int32, [n])
+        b_addr = addr(b)
+        assert b_addr != a_addr
+        assert np.array_equal(b, src)
+        a[:10] = -1  # writing one result never shows up in another
+        assert np.array_equal(b, src)
+        keep = view.copy()
+        del a
+        gc.collect()
+        c = cudashm.get_contents_as_numpy(h, np.int32, [n])  # `view` still holds a's buffer: not reused
+        c_addr = addr(c)
+        assert c_addr != a_addr and c_addr != b_addr
+        assert np.array_equal(view, keep)
+        del b, c, view
+        gc.collect()
+        d = cudashm.get_contents_as_numpy(h, np.int32, [n], offset=0)
+        assert np.array_equal(d, src)
+        assert addr(d) in (a_addr, b_addr, c_addr)  # a recycled buffer, not a new allocation
+        assert _host_pool.pool_stats()["held_bytes"] <= _host_pool._pool.limit
+        # offsets and other dtypes
+        e = cudashm.get_contents_as_numpy(h, np.uint8, [src.nbytes - 4096], offset=4096)
+        assert np.array_equal(e, src.view(np.uint8)[4096:])
+    finally:
+        cudashm.destroy_shared_memory_region(h)

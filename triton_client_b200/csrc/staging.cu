@@ -91,6 +91,8 @@ class CopyPool {
 struct StageRing {
   char* slot[kStageSlots] = {nullptr};
   cudaEvent_t ev[kStageSlots] = {nullptr};
+  bool busy[kStageSlots] = {false};  // ev[i] marks a DMA out of slot i that nobody has waited for yet
+  int next = 0;                      // slot the next host-to-device call starts with (oldest DMA first)
   bool ready = false;
 };
 
@@ -152,17 +154,20 @@ int staged_h2d(int device, void* dst_dev, const void* src_host, uint64_t bytes, 
   char* dst = static_cast<char*>(dst_dev);
   uint64_t off = 0;
   for (int k = 0; off < bytes; k++) {
-    const int i = k % kStageSlots;
+    const int i = (r->next + k) % kStageSlots;
     const size_t n = (size_t)std::min<uint64_t>(kStageSlot, bytes - off);
-    if (k >= kStageSlots) TCB_CUDA(cudaEventSynchronize(r->ev[i]));  // the DMA that last read this slot
+    // the DMA that last read this slot - of this call or of an earlier one: a call does not drain the
+    // ring when it ends (the source has been consumed by then, which is all the caller is promised), so
+    // the first slots of the next call fill while the last DMAs of this one are still running. Draining
+    // per call cost ~1 ms per call: 31 ms for 1.6 GB in one call, 40 ms in 8 calls, 67 ms in 32.
+    if (r->busy[i]) TCB_CUDA(cudaEventSynchronize(r->ev[i]));
     pool.copy(r->slot[i], src + off, n);
     TCB_CUDA(cudaMemcpyAsync(dst + off, r->slot[i], n, cudaMemcpyHostToDevice, s));
     TCB_CUDA(cudaEventRecord(r->ev[i], s));
+    r->busy[i] = true;
     off += n;
   }
-  // the ring is reused by the next call: its slots must be drained before the lock is released
-  const int used = (int)std::min<uint64_t>(kStageSlots, (bytes + kStageSlot - 1) / kStageSlot);
-  for (int i = 0; i < used; i++) TCB_CUDA(cudaEventSynchronize(r->ev[i]));
+  r->next = (int)((r->next + (bytes + kStageSlot - 1) / kStageSlot) % kStageSlots);
   return TCB_OK;
 }
 
@@ -178,6 +183,11 @@ int staged_d2h(int device, void* dst_host, const void* src_dev, uint64_t bytes, 
   auto issue = [&](uint64_t k) -> cudaError_t {
     const int i = (int)(k % kStageSlots);
     const size_t n = (size_t)std::min<uint64_t>(kStageSlot, bytes - k * kStageSlot);
+    if (r->busy[i]) {  // a host-to-device DMA of an earlier call may still be reading this slot
+      cudaError_t w = cudaEventSynchronize(r->ev[i]);
+      if (w != cudaSuccess) return w;
+      r->busy[i] = false;
+    }
     cudaError_t e = cudaMemcpyAsync(r->slot[i], src + k * kStageSlot, n, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaEventRecord(r->ev[i], s);
     return e;

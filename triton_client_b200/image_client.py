@@ -173,6 +173,20 @@ def preprocess_batch(images, format, dtype, c, h, w, scaling, out=None, out_offs
     return out, plan
 
 
+_mover = None
+
+
+def _out_mover():
+    """One helper thread per process for host-side result copies (numpy's copy and a CUDA event wait
+    both release the GIL)."""
+    global _mover
+    if _mover is None:
+        from concurrent.futures import ThreadPoolExecutor
+
+        _mover = ThreadPoolExecutor(max_workers=1, thread_name_prefix="tcb-out")
+    return _mover
+
+
 class HostBatchPipeline:
     """Pinned host images -> region (-> pinned host result), for batches of equally sized images.
 
@@ -252,6 +266,17 @@ class HostBatchPipeline:
         self.s_out.wait_stream(cur)
         base = self.stage.data_ptr()
         src_ptr = flat.ctypes.data
+        pending = []
+        if host_out is not None:
+            if getattr(self, "_out_events", None) is None:
+                self._out_events = [torch.cuda.Event() for _ in self.plans]
+            out_events = self._out_events
+            out_flat, pin_flat = host_out.reshape(-1).view(np.uint8), self._pin_out.numpy()
+
+            def move_out(j):
+                out_events[j].synchronize()
+                lo, hi = self.bounds[j] * self.out_bytes_per_image, self.bounds[j + 1] * self.out_bytes_per_image
+                np.copyto(out_flat[lo:hi], pin_flat[lo:hi])
         for k, plan in enumerate(self.plans):
             i0, i1 = self.bounds[k], self.bounds[k + 1]
             nb = (i1 - i0) * self.img_bytes
@@ -269,11 +294,14 @@ class HostBatchPipeline:
                 _lib.check(_lib.lib.TcbMemcpy(self.device, self._pin_out.data_ptr() + i0 * self.out_bytes_per_image,
                                               int(dst_ptr) + i0 * self.out_bytes_per_image, ob,
                                               self.s_out.cuda_stream, 0))
+                out_events[k].record(self.s_out)
+                # a helper thread waits for this piece's results and moves them on to the caller's array
+                # while the next pieces are staged and resampled, instead of one serial copy at the end
+                pending.append(_out_mover().submit(move_out, k))
         cur.wait_stream(self.s_in)
         cur.wait_stream(self.s_out)
-        if host_out is not None:
-            cur.synchronize()
-            np.copyto(host_out.reshape(-1).view(np.uint8), self._pin_out.numpy())
+        for f in pending:
+            f.result()
 
     def close(self):
         for p in self.plans:

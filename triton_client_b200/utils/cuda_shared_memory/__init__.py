@@ -21,6 +21,7 @@ from ... import _lib
 from ..._device import stream_ptr, to_host
 from .. import _dlpack
 from .._shared_memory_tensor import SharedMemoryTensor
+from . import _host_pool
 from ._utils import CudaSharedMemoryException, CudaSharedMemoryRegion
 
 allocated_shm_regions = []
@@ -85,7 +86,7 @@ def set_shared_memory_region(cuda_shm_handle, input_values, offset=0):
 
 
 def get_contents_as_numpy(cuda_shm_handle, datatype, shape, offset=0):
-    """Owning numpy array with the region's contents interpreted as ``datatype``/``shape``.
+    """New numpy array with the region's contents interpreted as ``datatype``/``shape``.
     Fixed-size dtypes copy only the bytes asked for; BYTES (``np.object_`` / ``np.bytes_``) is
     decoded on the device (chunked offset chase + gather) and only the payload comes back."""
     dev = cuda_shm_handle._device_id
@@ -99,10 +100,15 @@ def get_contents_as_numpy(cuda_shm_handle, datatype, shape, offset=0):
                 "The size of the shared memory region is insufficient to provide numpy array with requested size")
         if requested_byte_size == 0:
             return np.empty(shape, dtype=datatype)
-        result = np.empty(shape, dtype=datatype)
+        # large results land in a recycled page-locked buffer (see _host_pool): no first-touch page
+        # faults, no staging - the DMA engine writes the array the caller gets
+        result, host_ptr = _host_pool.leased_array(requested_byte_size, datatype, shape)
+        if result is None:
+            result = np.empty(shape, dtype=datatype)
+            host_ptr = result.ctypes.data
         try:
             stream = _get_or_create_global_cuda_stream(dev)
-            _lib.check(_lib.lib.TcbRegionGet(cuda_shm_handle._c_handle, start_pos, result.ctypes.data,
+            _lib.check(_lib.lib.TcbRegionGet(cuda_shm_handle._c_handle, start_pos, host_ptr,
                                              requested_byte_size, stream))
         except Exception as ex:
             raise CudaSharedMemoryException("failed to read cuda shared memory results") from ex
