@@ -11,6 +11,7 @@ results of /root/reference/src/python/examples/image_client.py:154-193. What run
   expressions on every uint8 value, which makes cast + scaling bit-exact for every dtype.
 """
 import ctypes
+import os
 
 import numpy as np
 
@@ -322,6 +323,38 @@ def _pil_to_array(img, c):
     return np.ascontiguousarray(a)
 
 
+_arrow = False if os.environ.get("TCB_PIL_ARROW", "1") == "0" else None  # False: never use Pillow's Arrow export
+
+
+def _pil_pixels(img, c):
+    """uint8 array [H, W, Cin] over the PIL image's own pixel memory where Pillow can export it without
+    a copy (its Arrow interface, Pillow >= 11.2: L as 1 byte, RGB and RGBA as the 4 bytes per pixel
+    Pillow stores them in), else ``_pil_to_array``. ``np.asarray(img)`` goes through ``tobytes()``,
+    which alone cost 150 of the 320 us of a 640x480 call. An RGB image arrives as RGBX: the kernels
+    take 4-channel sources and use the first three, which is exactly Pillow's RGBA -> RGB."""
+    global _arrow
+    img.load()  # a lazily opened file reports readonly = 1 until its pixels are decoded
+    # (images that wrap foreign memory - Image.frombuffer, memory-mapped files: `readonly` - are left to
+    # the copying route; Pillow 12.2's exporter crashes on them)
+    if (img.mode in ("L", "RGB", "RGBA") and hasattr(img, "__arrow_c_array__") and _arrow is not False
+            and not getattr(img, "readonly", 0)):
+        try:
+            if _arrow is None:
+                import pyarrow as _pa
+
+                _arrow = _pa
+            arr = _arrow.array(img)
+            flat = (arr.values if img.mode != "L" else arr).to_numpy(zero_copy_only=True)
+            w, h = img.size
+            if flat.dtype == np.uint8 and flat.size == w * h * (1 if img.mode == "L" else 4):
+                return flat.reshape(h, w, 1 if img.mode == "L" else 4)  # the view keeps the Arrow buffer alive
+        except ImportError:
+            _arrow = False
+        except Exception:
+            pass  # images spread over several memory blocks, exotic builds: the copying route below
+    return _pil_to_array(img, c)
+
+
 _plan_cache = {}
 
 
@@ -331,7 +364,7 @@ def preprocess(img, format, dtype, c, h, w, scaling, protocol=None):
     else (h, w, c). The plan and its two device buffers are kept per (device, geometry, dtype,
     scaling), so a repeated call costs one H2D copy, one kernel and one D2H copy."""
     c, h, w = int(c), int(h), int(w)
-    src = _pil_to_array(img, c)
+    src = _pil_pixels(img, c)
     dev = current_device()
     H, W, cin = src.shape
     key = (dev, W, H, cin, format == FORMAT_NCHW, dtype, c, h, w, scaling)
@@ -348,8 +381,16 @@ def preprocess(img, format, dtype, c, h, w, scaling, protocol=None):
     s = stream_ptr(dev)
     _lib.check(_lib.lib.TcbMemcpy(dev, d_src.data_ptr(), src.ctypes.data, src.size, s, 0))
     plan.run([d_src.data_ptr()], d_out.data_ptr(), plan.out_bytes_per_image, stream=s)
-    host = to_host(d_out.data_ptr(), plan.out_bytes_per_image, dev)  # synchronises
-    return host.view(plan.out_dtype).reshape(plan.out_shape[1:])
+    from .utils.cuda_shared_memory import _host_pool
+
+    # the result array lives in a recycled page-locked buffer when the pool has room: the DMA engine
+    # writes it directly, no staging and no first-touch page faults (cfg1: 322 -> see bench us per call)
+    out, out_ptr = _host_pool.leased_array(plan.out_bytes_per_image, plan.out_dtype, plan.out_shape[1:], min_bytes=64 << 10)
+    if out is None:
+        host = to_host(d_out.data_ptr(), plan.out_bytes_per_image, dev)  # synchronises
+        return host.view(plan.out_dtype).reshape(plan.out_shape[1:])
+    _lib.check(_lib.lib.TcbMemcpy(dev, out_ptr, d_out.data_ptr(), plan.out_bytes_per_image, s, 1))  # synchronises
+    return out
 
 
 # ---- the step after the decode: classification strings ----------------------

@@ -23,7 +23,8 @@ from ... import _lib
 
 MIN_BYTES = 2 << 20          # below this an ordinary array is as fast
 _GRANULE = 2 << 20
-_MAX_FREE = 4                # free buffers kept for reuse
+_SMALL_GRANULE = 64 << 10    # results below MIN_BYTES that ask for a lease anyway (preprocess(): one image)
+_MAX_FREE = 8                # free buffers kept for reuse
 
 
 class _Pool:
@@ -36,9 +37,9 @@ class _Pool:
         except ValueError:
             self.limit = 4 << 30
 
-    def take(self, nbytes):
+    def take(self, nbytes, min_bytes=MIN_BYTES):
         """(ptr, capacity) of a page-locked buffer of at least nbytes, or None (caller falls back)."""
-        if self.limit <= 0 or nbytes < MIN_BYTES:
+        if self.limit <= 0 or nbytes < min_bytes or nbytes <= 0:
             return None
         with self.lock:
             best = None
@@ -48,7 +49,8 @@ class _Pool:
             if best is not None:
                 cap, ptr = self.free.pop(best)
                 return ptr, cap
-            cap = (nbytes + _GRANULE - 1) // _GRANULE * _GRANULE
+            gran = _GRANULE if nbytes >= MIN_BYTES else _SMALL_GRANULE
+            cap = (nbytes + gran - 1) // gran * gran
             while self.free and self.held + cap > self.limit:  # make room: oldest free buffers first
                 c, p = self.free.pop(0)
                 _lib.lib.TcbHostFree(p)
@@ -77,9 +79,9 @@ class _Pool:
 _pool = _Pool()
 
 
-def leased_array(nbytes, datatype, shape):
+def leased_array(nbytes, datatype, shape, min_bytes=MIN_BYTES):
     """(numpy array over a pooled page-locked buffer, its address), or (None, None)."""
-    got = _pool.take(int(nbytes))
+    got = _pool.take(int(nbytes), min_bytes)
     if got is None:
         return None, None
     ptr, cap = got
