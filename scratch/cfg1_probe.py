@@ -21,7 +21,7 @@ pin = torch.empty(src.size, dtype=torch.uint8, pin_memory=True)
 print("copy to pinned          %.1f us" % t(lambda: np.copyto(pin.numpy(), src.reshape(-1))))
 print("H2D pinned 921 KB       %.1f us" % t(lambda: _lib.lib.TcbMemcpy(dev, d_src.data_ptr(), pin.data_ptr(), src.size, s, 1)))
 key = [k for k in ic._plan_cache][0]
-plan, a, b = ic._plan_cache[key]
+plan, a, b = ic._plan_cache[key][:3]
 def run():
     plan.run([a.data_ptr()], b.data_ptr(), plan.out_bytes_per_image, stream=s); _lib.lib.TcbStreamSync(dev, s)
 print("plan.run + sync         %.1f us" % t(run))
