@@ -355,8 +355,13 @@ class Ctx:
         kernel. `fns` is cycled: callers whose working set would otherwise stay in L2 pass several
         closures over different buffers. Max over ranks."""
         torch = self.torch
-        for i in range(warmup):
+        t0 = time.perf_counter()
+        i = 0
+        while i < warmup or time.perf_counter() - t0 < 0.05:  # short kernels: also long enough for the clocks to come up
             fns[i % len(fns)]()
+            i += 1
+            if i % 8 == 0:
+                torch.cuda.synchronize()
         torch.cuda.synchronize()
         self.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -886,6 +891,9 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     sampler.mark()
+    # stop polling here: nvidia-smi every 20 ms takes driver locks that the copy-heavy legs below
+    # (several hundred cudaMemcpyAsync / event calls per pass) would be timed against
+    clocks = sampler.stop() if rank == 0 else None
     cx.barrier()
     launches = _lib.kernel_launch_count() - launches0
     t_local = e0.elapsed_time(e1) * 1e-3
@@ -1013,8 +1021,6 @@ def main():
                     "value": cpu_bytes["all_cores"][d], "unit": "GB/s of serialized bytes", "cores": cpu_bytes["cores"],
                     "kind": cpu_bytes["kind"], "one_thread_gbs": cpu_bytes["one_thread"][d],
                     "sample": cpu_bytes["sample"] + " (the reference's Python loop, utils/__init__.py:193-276)"}
-    clocks = sampler.stop() if rank == 0 else None
-
     if rank == 0:
         algo = CFG3_ALGO_BYTES_PER_IMAGE * n
         kern_s = t_local / args.steps
