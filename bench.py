@@ -915,7 +915,7 @@ def main():
     parity = cx.sum_over_ranks(1.0 if parity_local else 0.0) == world
     del got
 
-    e2e_value = e2e_ok = h2d_ceiling_gbs = pageable = None
+    e2e_value = e2e_ok = h2d_ceiling_gbs = bidir_ceiling_gbs = pageable = None
     e2e_steps, in_bytes = 0, n * H * W * 3
     if args.no_e2e:
         del batch
@@ -936,10 +936,26 @@ def main():
 
         t_copy = cx.time_calls(bare_copy, steps=5, warmup=2)
         h2d_ceiling_gbs = world * in_bytes / t_copy / 1e9
-        del stage
+        # ... and with the result's read-back running against it on a second stream, which is what the
+        # pipeline does: both PCIe directions at once, on all ranks at once
+        s_a, s_b = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        d_res = torch.empty(out_bytes, dtype=torch.uint8, device=cx.device)
+
+        def bare_both():
+            here = torch.cuda.current_stream(dev)
+            s_a.wait_stream(here)
+            s_b.wait_stream(here)
+            _lib.check(_lib.lib.TcbMemcpy(dev, stage.data_ptr(), h_batch.data_ptr(), in_bytes, s_a.cuda_stream, 0))
+            _lib.check(_lib.lib.TcbMemcpy(dev, h_out.data_ptr(), d_res.data_ptr(), out_bytes, s_b.cuda_stream, 0))
+            here.wait_stream(s_a)
+            here.wait_stream(s_b)
+
+        t_both = cx.time_calls(bare_both, steps=5, warmup=2)
+        bidir_ceiling_gbs = world * in_bytes / t_both / 1e9
+        del stage, d_res
 
         pipe = HostBatchPipeline(n, W, H, 3, CFG3["format"], CFG3["dtype"], CFG3["c"], CFG3["h"], CFG3["w"],
-                                 CFG3["scaling"], device=dev, chunks=8)
+                                 CFG3["scaling"], device=dev, chunks=int(os.environ.get("TCB_BENCH_CHUNKS", "8")))
 
         def e2e_step():
             pipe.run(h_batch.data_ptr(), region._base_addr, out_bytes, h_out.data_ptr())
@@ -1045,6 +1061,10 @@ def main():
                     "h2d_ceiling": "bare pinned->device cudaMemcpyAsync of the same %d bytes on all %d ranks at once" % (in_bytes, world),
                     "h2d_achieved_gbs": e2e_value * H * W * 3 / 1e9,
                     "frac_of_h2d_ceiling": e2e_value * H * W * 3 / 1e9 / h2d_ceiling_gbs,
+                    "bidir_ceiling_gbs": bidir_ceiling_gbs,
+                    "bidir_ceiling": "the same copy with the %d-byte result read back on a second stream at the same time "
+                                     "(H2D GB/s until both are done)" % out_bytes,
+                    "frac_of_bidir_ceiling": e2e_value * H * W * 3 / 1e9 / bidir_ceiling_gbs,
                     "affinity": affinity, "from_pageable": pageable},
             "gpu_launches": launches, "clocks": clocks, "also": also,
             "wall_s": time.perf_counter() - t_start,
