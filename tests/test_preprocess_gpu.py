@@ -464,3 +464,48 @@ def test_large_mixed_batch_every_image_exact():
         for n, (i, j) in enumerate(zip(idx, pick)):
             assert np.array_equal(host[n], want[(int(i), int(j))]), (n, menu[int(i)], fmt, dt)
         plan.close()
+
+
+def test_plans_created_run_and_destroyed_from_several_threads():
+    """ctypes drops the GIL during calls: plans of different geometry are created, run many times and
+    destroyed by four threads at once (the fused-plan registry used to be an unlocked
+    process-global map; the fused state now lives in the plan). Every result must equal the oracle."""
+    import threading
+
+    import torch
+
+    from triton_client_b200.image_client import PreprocessPlan
+
+    geoms = [((1920, 1080), 2, "FP32", "VGG"), ((640, 480), 1, "FP16", "INCEPTION"),
+             ((500, 375), 2, "FP32", "NONE"), ((1280, 720), 1, "UINT8", "NONE")]
+    errors = []
+
+    def worker(k):
+        try:
+            (W, H), fmt, dtype, scaling = geoms[k]
+            rng = np.random.default_rng(8 + k)
+            imgs = [rng.integers(0, 256, (H, W, 3), dtype=np.uint8) for _ in range(3)]
+            want = [oracle_preprocess(a, 3, 224, 224, fmt, dtype, scaling) for a in imgs]
+            d_imgs = [torch.from_numpy(a).cuda() for a in imgs]
+            stream = torch.cuda.Stream()
+            for rep in range(6):
+                plan = PreprocessPlan([(W, H, 3)] * 3, fmt, dtype, 3, 224, 224, scaling, device=0)
+                out = torch.empty(3 * plan.out_bytes_per_image, dtype=torch.uint8, device="cuda")
+                for _ in range(5):
+                    plan.run([t.data_ptr() for t in d_imgs], out.data_ptr(), out.numel(), stream=stream.cuda_stream)
+                stream.synchronize()
+                got = out.cpu().numpy()
+                per = plan.out_bytes_per_image
+                for i in range(3):
+                    if got[i * per:(i + 1) * per].tobytes() != np.ascontiguousarray(want[i]).tobytes():
+                        errors.append("thread %d rep %d image %d differs" % (k, rep, i))
+                plan.close()
+        except Exception as ex:  # noqa: BLE001
+            errors.append("thread %d: %r" % (k, ex))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(len(geoms))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    assert not errors, errors[:3]
