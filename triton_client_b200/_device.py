@@ -55,8 +55,16 @@ def to_device_u8(buf, device):
 
 def to_host(ptr, nbytes, device):
     """D2H copy of `nbytes` from a device pointer into a new uint8 numpy array (synchronous)."""
-    out = np.empty(int(nbytes), dtype=np.uint8)
+    nbytes = int(nbytes)
+    if nbytes >= (1 << 20):  # large: a recycled page-locked buffer (no staging, no first-touch page faults)
+        from .utils.cuda_shared_memory import _host_pool
+
+        out, host_ptr = _host_pool.leased_array(nbytes, np.uint8, [nbytes], min_bytes=1 << 20)
+        if out is not None:
+            _lib.check(_lib.lib.TcbMemcpy(device, host_ptr, ptr, nbytes, stream_ptr(device), 1))
+            return out
+    out = np.empty(nbytes, dtype=np.uint8)
     if nbytes:
-        _lib.check(_lib.lib.TcbMemcpy(device, out.ctypes.data, ptr, int(nbytes),
+        _lib.check(_lib.lib.TcbMemcpy(device, out.ctypes.data, ptr, nbytes,
                                       stream_ptr(device), 1))
     return out

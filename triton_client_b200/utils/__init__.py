@@ -175,6 +175,45 @@ def _dst_of(obj, offset):
 # ---- reference-facing API -----------------------------------------------------------------------
 
 
+try:  # the two per-element loops in C (csrc/pyobj.c, built next to libtcb200.so by `make`)
+    from .. import _pyobj
+except ImportError:  # not built (no Python headers): the same loops in Python below
+    _pyobj = None
+
+
+def _gather_objects(input_tensor, dev):
+    """(device payload tensor, device int64 lengths tensor) of an np.object_ tensor, C order: the
+    host half of utils/__init__.py:226-243 of the reference. With _pyobj the elements are visited once
+    in C and their bytes copied by a few threads straight into a pooled page-locked buffer."""
+    import torch
+
+    n = int(input_tensor.size)
+    if _pyobj is None:
+        elems = _elements_as_bytes(input_tensor)
+        lens = np.fromiter(map(len, elems), dtype=np.int64, count=n)
+        if lens.size and int(lens.max()) > 0xFFFFFFFF:
+            raise struct.error("'I' format requires 0 <= number <= 4294967295")
+        return to_device_u8(b"".join(elems), dev), torch.from_numpy(lens).to("cuda:%d" % dev)
+    from .cuda_shared_memory import _host_pool
+
+    flat = np.ascontiguousarray(input_tensor.ravel(order="C"))  # PyObject* items, kept alive until copied
+    lens = np.empty(n, dtype=np.int64)
+    total, handle = _pyobj.prepare(flat.ctypes.data, n, lens.ctypes.data)
+    if n and int(lens.max()) > 0xFFFFFFFF:
+        raise struct.error("'I' format requires 0 <= number <= 4294967295")
+    d_lens = torch.from_numpy(lens).to("cuda:%d" % dev)
+    d_blob = torch.empty(max(total, 1), dtype=torch.uint8, device="cuda:%d" % dev)
+    if total:
+        stage, ptr = _host_pool.leased_array(total, np.uint8, [total], min_bytes=1 << 20)
+        if stage is None:
+            stage = np.empty(total, dtype=np.uint8)
+            ptr = stage.ctypes.data
+        _pyobj.copy(handle, ptr, total, 6)
+        _lib.check(_lib.lib.TcbMemcpy(dev, d_blob.data_ptr(), ptr, total, stream_ptr(dev), 1))
+        del stage
+    return d_blob, d_lens
+
+
 def _elements_as_bytes(input_tensor):
     """Host-side normalisation of an object array (utils/__init__.py:229-237): exact ``bytes``
     pass through, everything else is ``str()``-encoded as UTF-8; logical C order."""
@@ -198,13 +237,7 @@ def serialize_byte_tensor_to(out, input_tensor, out_offset=0, device=None):
     dev = (_device_of(out) if out is not None else current_device()) if device is None else device
     n = int(input_tensor.size)
     if input_tensor.dtype == np.object_:
-        elems = _elements_as_bytes(input_tensor)
-        lens = np.fromiter(map(len, elems), dtype=np.int64, count=n)
-        blob = b"".join(elems)
-        if lens.size and int(lens.max()) > 0xFFFFFFFF:
-            raise struct.error("'I' format requires 0 <= number <= 4294967295")
-        d_blob = to_device_u8(blob, dev)
-        d_lens = torch.from_numpy(lens).to("cuda:%d" % dev, non_blocking=False)
+        d_blob, d_lens = _gather_objects(input_tensor, dev)
         if out is None:
             return serialize_to_device(d_blob, d_lens, None, 0, dev)
         _, total = serialize_to_device(d_blob, d_lens, out, out_offset, dev)
@@ -244,10 +277,15 @@ def serialize_byte_tensor(input_tensor):
 def _object_array_from(offsets, payload):
     """1-D object array of ``bytes`` from host offsets / payload (the unavoidable per-element
     Python object creation)."""
+    n = int(offsets.size) - 1
+    arr = np.empty(n, dtype=np.object_)
+    if _pyobj is not None:
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        pay = np.ascontiguousarray(payload, dtype=np.uint8)
+        _pyobj.scatter(pay.ctypes.data, off.ctypes.data, n, arr.ctypes.data)
+        return arr
     blob = payload.tobytes()
     off = offsets.tolist()
-    n = len(off) - 1
-    arr = np.empty(n, dtype=np.object_)
     arr[:] = [blob[off[i]:off[i + 1]] for i in range(n)]
     return arr
 
