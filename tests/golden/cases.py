@@ -66,10 +66,26 @@ PREPROCESS_CASES = [
 ]
 
 
+# Source modes the kernels do not take as they are: the reference converts them with Pillow
+# (image_client.py:161-164: img.convert("L") / img.convert("RGB")) before the resize, and so does the
+# drop-in (image_client._pil_to_array) - file-format glue, not the resampling path. These cases pin
+# that the glue is the same.
+MODE_CASES = [
+    _case("m_cmyk_to_rgb", 50, 320, 240, NCHW, "FP32", "INCEPTION", mode="CMYK"),
+    _case("m_la_to_rgb", 51, 333, 211, NHWC, "FP16", "VGG", mode="LA"),
+    _case("m_la_to_l", 52, 320, 240, NCHW, "FP32", "NONE", c=1, mode="LA"),
+    _case("m_palette_to_rgb", 53, 640, 480, NCHW, "FP32", "VGG", mode="P"),
+    _case("m_palette_to_l", 54, 200, 300, NHWC, "UINT8", "NONE", c=1, mode="P"),
+    _case("m_ycbcr_to_rgb", 55, 500, 375, NHWC, "FP32", "INCEPTION", mode="YCbCr"),
+    _case("m_cmyk_to_l", 56, 150, 100, NCHW, "FP16", "INCEPTION", c=1, mode="CMYK"),
+]
+
+
 def make_image(case):
-    """uint8 source array: [H, W, 3] for RGB, [H, W] for L, [H, W, 4] for RGBA."""
+    """uint8 source array: [H, W, 3] for RGB, [H, W] for L, [H, W, 4] for RGBA (and the raw planes of
+    the other modes: CMYK 4, LA 2, P 1 index plane, YCbCr 3)."""
     H, W = case["H"], case["W"]
-    nch = {"RGB": 3, "L": 1, "RGBA": 4}[case["mode"]]
+    nch = {"RGB": 3, "L": 1, "RGBA": 4, "CMYK": 4, "LA": 2, "P": 1, "YCbCr": 3}[case["mode"]]
     kind = case["kind"]
     if kind == "uniform":
         a = np.random.default_rng(case["seed"]).integers(0, 256, (H, W, nch), dtype=np.uint8)
@@ -95,6 +111,13 @@ def make_image(case):
 def to_pil(src, case):
     from PIL import Image
 
+    if case["mode"] == "P":  # an index plane + a palette drawn from the case's seed
+        img = Image.fromarray(src, "P")
+        pal = np.random.default_rng(case["seed"] + 1000).integers(0, 256, 768, dtype=np.uint8)
+        img.putpalette(pal.tolist())
+        return img
+    if case["mode"] in ("CMYK", "LA", "YCbCr"):
+        return Image.frombytes(case["mode"], (case["W"], case["H"]), np.ascontiguousarray(src).tobytes())
     return Image.fromarray(src, case["mode"])
 
 

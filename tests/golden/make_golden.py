@@ -58,6 +58,20 @@ def main():
             small[case["name"]] = outc
     with open(os.path.join(HERE, "preprocess_golden.json"), "w") as f:
         json.dump(gold, f, indent=1)
+    # ---- source modes that Pillow converts before the resize (CMYK, LA, P, YCbCr) --------------
+    mg = {"env": env, "cases": []}
+    for case in cases.MODE_CASES:
+        src = cases.make_image(case)
+        img = cases.to_pil(src, case)
+        outc = np.ascontiguousarray(pre(img, case["format"], case["dtype"], case["c"], case["h"], case["w"],
+                                        case["scaling"], "grpc"))
+        conv = np.asarray(img.convert("L" if case["c"] == 1 else "RGB"))
+        rec = dict(case)
+        rec.update({"src_sha256": sha(np.ascontiguousarray(src).tobytes()), "converted_sha256": sha(np.ascontiguousarray(conv).tobytes()),
+                    "out_sha256": sha(outc.tobytes()), "out_dtype": str(outc.dtype), "out_shape": list(outc.shape)})
+        mg["cases"].append(rec)
+    with open(os.path.join(HERE, "preprocess_modes_golden.json"), "w") as f:
+        json.dump(mg, f, indent=1)
     np.savez_compressed(os.path.join(HERE, "preprocess_small.npz"), **small)
 
     # ---- BYTES ------------------------------------------------------------------------------

@@ -56,6 +56,23 @@ def test_c_oracle_matches_reference_golden(rec):
         assert np.array_equal(out, SMALL[rec["name"]])
 
 
+MODES = json.load(open(os.path.join(GOLD, "preprocess_modes_golden.json")))
+
+
+@pytest.mark.parametrize("rec", MODES["cases"], ids=[c["name"] for c in MODES["cases"]])
+def test_modes_converted_by_pillow_then_oracle_matches_reference_golden(rec):
+    """CMYK / LA / P / YCbCr sources: the reference lets Pillow convert them to L or RGB before the
+    resize (image_client.py:161-164) and so does the product; from there on it is the oracle's path."""
+    src = cases.make_image(rec)
+    assert sha(np.ascontiguousarray(src).tobytes()) == rec["src_sha256"]
+    conv = np.asarray(cases.to_pil(src, rec).convert("L" if rec["c"] == 1 else "RGB"))
+    if sha(np.ascontiguousarray(conv).tobytes()) != rec["converted_sha256"]:
+        pytest.skip("this Pillow converts the mode differently from the one the goldens were made with")
+    u8, out = oracle_preprocess_c(conv, rec)
+    assert str(out.dtype) == rec["out_dtype"] and list(out.shape) == rec["out_shape"]
+    assert sha(out.tobytes()) == rec["out_sha256"]
+
+
 _NUMPY_CASES = [c for c in PRE["cases"] if c["W"] * c["H"] <= 1280 * 720]
 
 

@@ -466,6 +466,25 @@ def test_large_mixed_batch_every_image_exact():
         plan.close()
 
 
+MODES = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "preprocess_modes_golden.json")))
+
+
+@pytest.mark.parametrize("rec", MODES["cases"], ids=[c["name"] for c in MODES["cases"]])
+def test_preprocess_dropin_other_source_modes_match_reference_golden(rec):
+    """CMYK / LA / palette / YCbCr images through the drop-in: Pillow converts (as in the reference),
+    the GPU resamples; the result must be the reference's."""
+    from triton_client_b200.image_client import preprocess
+
+    src = cases.make_image(rec)
+    img = cases.to_pil(src, rec)
+    conv = np.asarray(img.convert("L" if rec["c"] == 1 else "RGB"))
+    if sha(np.ascontiguousarray(conv).tobytes()) != rec["converted_sha256"]:
+        pytest.skip("this Pillow converts the mode differently from the one the goldens were made with")
+    out = np.ascontiguousarray(preprocess(img, rec["format"], rec["dtype"], rec["c"], rec["h"], rec["w"], rec["scaling"], "grpc"))
+    assert str(out.dtype) == rec["out_dtype"] and list(out.shape) == rec["out_shape"]
+    assert sha(out.tobytes()) == rec["out_sha256"]
+
+
 def test_plans_created_run_and_destroyed_from_several_threads():
     """ctypes drops the GIL during calls: plans of different geometry are created, run many times and
     destroyed by four threads at once (the fused-plan registry used to be an unlocked
