@@ -767,9 +767,38 @@ def bench_bytes_api(cx):
             td.append(time.perf_counter() - t0)
         ok = bool(nb == total and back.shape == (N,) and back[0] == arr[0] and back[N - 1] == arr[N - 1]
                   and all(back[i] == arr[i] for i in range(0, N, 997)))
+        # a request's handful of strings: latency of the host-to-host drop-ins, next to the reference's loops
+        from oracle import bytes_codec as obc
+
+        def med_us(fn, reps):
+            for _ in range(10):
+                fn()
+            xs = []
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                fn()
+                xs.append(time.perf_counter() - t0)
+            return float(np.median(xs) * 1e6)
+
+        small = {}
+        for k in (1, 16, 256):
+            a = np.empty(k, dtype=np.object_)
+            for i in range(k):
+                a[i] = b"0.%06d:%d:label number %d" % (i * 7919 % 1000000, i, i)
+            ser = u.serialize_byte_tensor(a).item()
+            small[str(k)] = {"serialize_us": med_us(lambda: u.serialize_byte_tensor(a), 200),
+                             "deserialize_us": med_us(lambda: u.deserialize_bytes_tensor(ser), 200),
+                             "cpu_serialize_us": med_us(lambda: obc.serialize_elements(a), 50),
+                             "cpu_deserialize_us": med_us(lambda: obc.deserialize_stream(ser), 50),
+                             "equal": bool(ser == obc.serialize_elements(a)
+                                           and u.deserialize_bytes_tensor(ser).tolist() == obc.deserialize_stream(ser))}
         return {"object_array_to_region_ms": min(ts) * 1e3, "region_to_object_array_ms": min(td) * 1e3,
                 "serialize_gbs": total / min(ts) / 1e9, "deserialize_gbs": total / min(td) / 1e9, "elements": N,
                 "sampled_equal": ok,
+                "small_tensors": small,
+                "small_tensors_note": "median us per call of serialize_byte_tensor / deserialize_bytes_tensor (host bytes in, "
+                                      "host bytes out) for 1 / 16 / 256 short strings; cpu_* = the reference's Python loops "
+                                      "(oracle port). Launch-latency-bound: one kernel launch and one synchronisation each",
                 "config": {"workload": "cfg2 recipe as a 1-D np.object_ array of 1M bytes objects -> serialize_byte_tensor_to("
                                        "region); get_contents_as_numpy(region, np.object_, [1M]); wall clock, best of 3"}}
     finally:

@@ -244,7 +244,13 @@ int TcbBytesSerializeFixedWidth(int device_id, const void* rows_dev, uint32_t wi
  * offsets_dev    : int64[offsets_capacity + 1]; element i is payload[offsets[i]:offsets[i+1]]
  * payload_dev    : receives the payloads back to back (capacity payload_capacity bytes)
  * n_elements_host, payload_bytes_host : results (host). The call synchronises the stream.
- * Returns TCB_ERR_TRUNCATED where the reference raises struct.error. */
+ * Returns TCB_ERR_TRUNCATED where the reference raises struct.error.
+ * A stream of at most 16 KiB (a request's handful of strings) is decoded by one single-CTA kernel
+ * launch and one host round trip instead of the seven-launch chunked path. For the BYTES entry
+ * points "device" pointers may also be page-locked host memory (cudaHostAlloc / cudaHostRegister:
+ * device-addressable under unified addressing): the Python layer serialises small tensors straight
+ * out of and into one pinned staging buffer that way. Keep a stream to be decoded in device memory
+ * though - the decoder follows a chain of dependent loads, ~1.5 us per element over PCIe. */
 int TcbBytesDeserialize(int device_id, const void* stream_dev, uint64_t stream_bytes,
                         int64_t max_elements, int64_t* offsets_dev, uint64_t offsets_capacity,
                         void* payload_dev, uint64_t payload_capacity, void* workspace_dev,

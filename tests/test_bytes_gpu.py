@@ -317,3 +317,78 @@ def test_tile_larger_than_2gib_takes_the_64bit_copy():
     offsets, payload = u.deserialize_from_device(out, total)
     assert np.array_equal(np.diff(offsets.cpu().numpy()), lens_h)
     assert torch.equal(payload, blob)
+
+
+def test_single_launch_path_for_streams_of_one_chunk():
+    """Streams of at most 16 KiB decoded by TcbBytesDeserialize take k_des_tiny (one CTA, one launch):
+    every cut point of a small stream, element limits, garbage tails, unaligned stream pointers and
+    capacity errors against the oracle's walk (utils/__init__.py:262-276 / cuda_shared_memory:305-323)."""
+    import ctypes
+
+    import torch
+
+    from triton_client_b200 import _lib
+
+    rng = np.random.default_rng(77)
+    ws_bytes = int(_lib.lib.TcbBytesDeserializeWorkspace(16384))
+    ws = torch.empty(max(ws_bytes, 256), dtype=torch.uint8, device="cuda")
+
+    def decode(stream, max_elements=-1, mis=0, ocap=None, pcap=None):
+        buf = torch.empty(stream.size + 64, dtype=torch.uint8, device="cuda")
+        buf[mis:mis + stream.size] = torch.from_numpy(stream).cuda()
+        ocap = stream.size // 4 + 1 if ocap is None else ocap
+        pcap = stream.size if pcap is None else pcap
+        offs = torch.full((ocap + 2,), -7, dtype=torch.int64, device="cuda")
+        pay = torch.full((pcap + 8,), 0xA5, dtype=torch.uint8, device="cuda")
+        n, pb = ctypes.c_uint64(0), ctypes.c_uint64(0)
+        before = _lib.kernel_launch_count()
+        rc = _lib.lib.TcbBytesDeserialize(0, buf.data_ptr() + mis, stream.size, max_elements, offs.data_ptr(), ocap,
+                                          pay.data_ptr(), pcap, ws.data_ptr(), int(ws.numel()), ctypes.byref(n),
+                                          ctypes.byref(pb), None)
+        launches = _lib.kernel_launch_count() - before
+        return rc, int(n.value), int(pb.value), offs.cpu().numpy(), pay.cpu().numpy(), launches
+
+    for trial in range(12):
+        n = int(rng.integers(1, 120))
+        lens = rng.integers(0, 90, n)
+        lens[rng.integers(0, n)] = 0
+        blob = rng.integers(0, 256, int(lens.sum()), dtype=np.uint8)
+        stream = clib.bytes_serialize(blob, lens.astype(np.int64))
+        assert stream.size <= 16384
+        want_off = np.concatenate(([0], np.cumsum(lens)))
+        rc, got_n, got_pb, offs, pay, launches = decode(stream, mis=trial % 5)
+        assert rc == 0 and launches == 1
+        assert got_n == n and got_pb == blob.size
+        assert np.array_equal(offs[:n + 1], want_off) and (offs[n + 1:] == -7).all()
+        assert np.array_equal(pay[:blob.size], blob) and (pay[blob.size:] == 0xA5).all()
+        # element limit (get_contents_as_numpy semantics): m elements, whatever follows is ignored
+        m = int(rng.integers(1, n + 1))
+        rc, got_n, got_pb, offs, pay, _ = decode(np.concatenate((stream, rng.integers(0, 256, 9, dtype=np.uint8))), m)
+        assert rc == 0 and got_n == m and got_pb == want_off[m]
+        assert np.array_equal(offs[:m + 1], want_off[:m + 1]) and np.array_equal(pay[:got_pb], blob[:got_pb])
+        # more elements asked for than the buffer holds: the reference unpacks past the end
+        assert decode(stream, n + 1)[0] == _lib.TCB_ERR_TRUNCATED
+        # every kind of cut: inside a prefix, inside a payload, exactly between elements
+        for cut in sorted(set(rng.integers(1, stream.size, 6).tolist())):
+            part = stream[:cut]
+            try:
+                w_blob, w_off = bc.deserialize_blob(part)
+                ok = True
+            except bc.OracleError:
+                ok = False
+            rc, got_n, got_pb, offs, pay, _ = decode(part)
+            if ok:
+                assert rc == 0 and got_n == w_off.size - 1 and np.array_equal(offs[:got_n + 1], w_off)
+                assert np.array_equal(pay[:got_pb], w_blob)
+            else:
+                assert rc == _lib.TCB_ERR_TRUNCATED
+        # capacities
+        if n > 1:
+            assert decode(stream, ocap=n - 1)[0] == _lib.TCB_ERR_OUT_OF_RANGE
+        if blob.size > 1:
+            rc, _, _, _, pay, _ = decode(stream, pcap=blob.size - 1)
+            assert rc == _lib.TCB_ERR_OUT_OF_RANGE and (pay == 0xA5).all()
+    # exactly one chunk, all-zero lengths (4096 empty elements)
+    z = np.zeros(16384, dtype=np.uint8)
+    rc, got_n, got_pb, offs, _, launches = decode(z)
+    assert rc == 0 and launches == 1 and got_n == 4096 and got_pb == 0 and not offs[:4097].any()

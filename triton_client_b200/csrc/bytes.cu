@@ -1224,6 +1224,59 @@ k_des_gather_long(const uint8_t* __restrict__ stream, const long long* __restric
   }
 }
 
+// A stream that fits one chunk (a request's handful of strings): everything in one CTA and one launch.
+// The stream is staged in shared memory, thread 0 follows the chain there (the general path chases a
+// single chunk with a single lane as well, but from global memory and behind six more launches and
+// two host round trips), offsets follow from the header positions alone (element i starts at
+// header_i - 4 i of the payload), then all threads move the payload. hdr[DW_STATUS]: 0 ok,
+// 2 truncated, 3 offsets capacity, 4 payload capacity; hdr[DW_NELEM], hdr[DW_PAYLOAD] as usual.
+constexpr int kTinyThreads = 256;
+
+__global__ void __launch_bounds__(kTinyThreads)
+k_des_tiny(const uint8_t* __restrict__ stream, unsigned int S, long long max_elements,
+           long long* __restrict__ offsets, unsigned long long offsets_capacity, uint8_t* __restrict__ payload,
+           unsigned long long payload_capacity, unsigned long long* __restrict__ hdr) {
+  __shared__ __align__(16) uint8_t s_stream[kDesChunk + 16];
+  __shared__ unsigned short s_pos[kDesChunk / 4 + 1];
+  __shared__ unsigned int s_n, s_status, s_end;
+  const int tid = threadIdx.x;
+  unsigned int bulk = 0;
+  if ((reinterpret_cast<uintptr_t>(stream) & 15) == 0) {
+    bulk = S & ~15u;
+    for (unsigned int i = tid * 16u; i < bulk; i += kTinyThreads * 16u)
+      *reinterpret_cast<uint4*>(s_stream + i) = __ldg(reinterpret_cast<const uint4*>(stream + i));
+  }
+  for (unsigned int i = bulk + tid; i < S; i += kTinyThreads) s_stream[i] = stream[i];
+  __syncthreads();
+  if (tid == 0) {
+    unsigned int pos = 0, n = 0, status = 0;
+    while (pos < S && (max_elements < 0 || (long long)n < max_elements)) {
+      if (pos + 4 > S) { status = 2; break; }
+      const unsigned int len = (unsigned int)s_stream[pos] | ((unsigned int)s_stream[pos + 1] << 8) |
+                               ((unsigned int)s_stream[pos + 2] << 16) | ((unsigned int)s_stream[pos + 3] << 24);
+      if (len > S - pos - 4) { status = 2; break; }
+      s_pos[n++] = (unsigned short)pos;
+      pos += 4 + len;
+    }
+    if (status == 0 && max_elements > 0 && (long long)n < max_elements) status = 2;  // asked for more than there is
+    if (status == 0 && n > offsets_capacity) status = 3;
+    if (status == 0 && (unsigned long long)(pos - 4 * n) > payload_capacity) status = 4;
+    s_n = n; s_status = status; s_end = pos;
+    hdr[DW_STATUS] = status; hdr[DW_NELEM] = n; hdr[DW_PAYLOAD] = pos - 4 * n;
+  }
+  __syncthreads();
+  if (s_status != 0) return;
+  const unsigned int n = s_n, end = s_end;
+  for (unsigned int i = tid; i <= n; i += kTinyThreads) offsets[i] = (long long)((i < n ? s_pos[i] : end) - 4 * i);
+  // payload: one warp per element, a byte per lane and round (elements here are short)
+  const int lane = tid & 31, warp = tid >> 5;
+  for (unsigned int i = warp; i < n; i += kTinyThreads / 32) {
+    const unsigned int a = s_pos[i] + 4u, b = i + 1 < n ? s_pos[i + 1] : end;
+    uint8_t* dst = payload + (a - 4u * (i + 1));
+    for (unsigned int j = a + lane; j < b; j += 32) dst[j - a] = s_stream[j];
+  }
+}
+
 static uint64_t des_chunks(uint64_t stream_bytes) { return (stream_bytes + kDesChunk - 1) / kDesChunk; }
 
 }  // namespace tcb
@@ -1338,6 +1391,29 @@ static int des_impl(int mode, int device_id, const void* stream_dev, uint64_t st
     return set_error(TCB_ERR_TRUNCATED, "TcbBytesDeserialize: empty buffer but %lld elements requested",
                      (long long)max_elements);
   TCB_CHECK_ARG(stream_dev != nullptr && workspace_dev != nullptr, "TcbBytesDeserialize: NULL stream/workspace");
+  if (mode == DES_ALL && stream_bytes <= (uint64_t)kDesChunk && workspace_bytes >= 256 &&
+      reinterpret_cast<uintptr_t>(workspace_dev) % 8 == 0) {  // one chunk: one launch, one round trip
+    unsigned long long* th = reinterpret_cast<unsigned long long*>(workspace_dev);
+    k_des_tiny<<<1, kTinyThreads, 0, s>>>(static_cast<const uint8_t*>(stream_dev), (unsigned int)stream_bytes,
+                                          (long long)max_elements, reinterpret_cast<long long*>(offsets_dev),
+                                          offsets_capacity, static_cast<uint8_t*>(payload_dev), payload_capacity, th);
+    count_launch();
+    unsigned long long h[DW_HEADER_WORDS];
+    TCB_CUDA(cudaMemcpyAsync(h, th, sizeof(h), cudaMemcpyDeviceToHost, s));
+    TCB_CUDA(cudaStreamSynchronize(s));
+    if (h[DW_STATUS] == 2)
+      return set_error(TCB_ERR_TRUNCATED, "TcbBytesDeserialize: buffer ends inside an element after %llu elements",
+                       (unsigned long long)h[DW_NELEM]);
+    if (h[DW_STATUS] == 3)
+      return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesDeserialize: %llu elements exceed offsets capacity %llu",
+                       (unsigned long long)h[DW_NELEM], (unsigned long long)offsets_capacity);
+    if (h[DW_STATUS] == 4)
+      return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesDeserialize: payload of %llu bytes exceeds capacity %llu",
+                       (unsigned long long)h[DW_PAYLOAD], (unsigned long long)payload_capacity);
+    *n_elements_host = h[DW_NELEM];
+    if (payload_bytes_host) *payload_bytes_host = h[DW_PAYLOAD];
+    return TCB_OK;
+  }
   const uint64_t need = TcbBytesDeserializeWorkspace(stream_bytes);
   if (workspace_bytes < need)
     return set_error(TCB_ERR_OUT_OF_RANGE, "TcbBytesDeserialize: workspace needs %llu bytes, got %llu",

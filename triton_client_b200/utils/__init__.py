@@ -175,6 +175,8 @@ def _dst_of(obj, offset):
 # ---- reference-facing API -----------------------------------------------------------------------
 
 
+from . import _small
+
 try:  # the two per-element loops in C (csrc/pyobj.c, built next to libtcb200.so by `make`)
     from .. import _pyobj
 except ImportError:  # not built (no Python headers): the same loops in Python below
@@ -269,6 +271,12 @@ def serialize_byte_tensor(input_tensor):
         return np.empty([0], dtype=np.object_)
     if (input_tensor.dtype != np.object_) and (input_tensor.dtype.type != np.bytes_):
         raise_error("cannot serialize bytes tensor: invalid datatype")
+    if _pyobj is not None and input_tensor.dtype == np.object_ and input_tensor.size <= _small.MAX_ELEMENTS:
+        # a handful of strings: the kernel works straight on page-locked host memory (utils/_small.py)
+        flat = np.ascontiguousarray(input_tensor.ravel(order="C"))
+        flattened = _small.serialize_objects(_pyobj, flat, current_device())
+        if flattened is not None:
+            return np.asarray(flattened, dtype=np.object_)
     out_t, total = serialize_byte_tensor_to(None, input_tensor)
     flattened = to_host(out_t.data_ptr(), total, out_t.device.index).tobytes()
     return np.asarray(flattened, dtype=np.object_)
@@ -298,6 +306,9 @@ def deserialize_bytes_tensor(encoded_tensor):
     if len(buf) == 0:
         return np.array([], dtype=np.object_)
     dev = current_device()
+    small = _small.deserialize_stream(buf, dev)
+    if small is not None:
+        return _object_array_from(small[0], small[1])
     d_stream = to_device_u8(buf, dev)
     offsets, payload = deserialize_from_device(d_stream, len(buf), -1, 0, dev)
     h_off = to_host(offsets.data_ptr(), offsets.numel() * 8, dev).view(np.int64)
