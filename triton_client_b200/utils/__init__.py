@@ -373,6 +373,9 @@ def serialize_bf16_tensor(input_tensor):
     if input_tensor.dtype != np.float32:
         raise_error("cannot serialize bf16 tensor: invalid datatype")
     dev = current_device()
+    small = _small.bf16_serialize(np.ascontiguousarray(input_tensor), dev)
+    if small is not None:
+        return np.asarray(small, dtype=np.object_)
     d_src = to_device_u8(np.ascontiguousarray(input_tensor), dev)
     n = int(input_tensor.size)
     out = torch.empty(2 * n, dtype=torch.uint8, device="cuda:%d" % dev)
@@ -394,6 +397,9 @@ def deserialize_bf16_tensor(encoded_tensor):
         raise struct.error("unpack_from requires a buffer of at least %d bytes for unpacking 2 bytes at offset %d "
                            "(actual buffer size is %d)" % (len(buf) + 1, len(buf) - 1, len(buf)))
     dev = current_device()
+    small = _small.bf16_deserialize(buf, dev)
+    if small is not None:
+        return small.reshape(-1, 1)
     d_stream = to_device_u8(buf, dev)
     out = deserialize_bf16_from_device(d_stream, len(buf), 0, None, dev, sync=False)
     host = to_host(out.data_ptr(), out.numel() * 4, dev).view(np.float32)

@@ -93,3 +93,42 @@ def deserialize_stream(buf, dev):
         offsets = view[o:o + 8 * (int(n.value) + 1)].view(np.int64).copy()
         payload = view[p:p + int(pb.value)].copy()
         return offsets, payload
+
+
+BF16_MAX_ELEMENTS = 256 << 10  # 1 MiB of float32 in, 512 KiB out: both fit the stage
+
+
+def bf16_serialize(values, dev):
+    """bfloat16 wire bytes of the C-contiguous float32 ndarray `values` (any shape), or None when it is
+    too large for this path. One launch that reads and writes the page-locked stage, one sync."""
+    n = int(values.size)
+    if n > BF16_MAX_ELEMENTS:
+        return None
+    with _lock:
+        pin, view = _get(dev)[:2]
+        base = pin.data_ptr()
+        view[:4 * n] = values.reshape(-1).view(np.uint8)
+        o = (4 * n + 15) & ~15
+        s = stream_ptr(dev)
+        _lib.check(_lib.lib.TcbBf16Serialize(dev, base, n, base + o, 2 * n, s))
+        _lib.check(_lib.lib.TcbStreamSync(dev, s))
+        return view[o:o + 2 * n].tobytes()
+
+
+def bf16_deserialize(buf, dev):
+    """float32 ndarray [n] for the bfloat16 wire bytes `buf` (even length), or None when too large."""
+    nbytes = len(buf)
+    if nbytes > 2 * BF16_MAX_ELEMENTS:
+        return None
+    with _lock:
+        pin, view = _get(dev)[:2]
+        base = pin.data_ptr()
+        view[:nbytes] = np.frombuffer(buf, dtype=np.uint8)
+        o = (nbytes + 15) & ~15
+        s = stream_ptr(dev)
+        rc = _lib.lib.TcbBf16Deserialize(dev, base, nbytes, base + o, 2 * nbytes, s)
+        if rc == _lib.TCB_ERR_TRUNCATED:
+            raise struct.error(_lib.last_error())
+        _lib.check(rc)
+        _lib.check(_lib.lib.TcbStreamSync(dev, s))
+        return view[o:o + 2 * nbytes].view(np.float32).copy()
