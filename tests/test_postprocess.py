@@ -135,3 +135,21 @@ def test_host_path_for_non_bytes_outputs_matches_oracle():
             return np.array([["0.5:1:a", "0.25:2:b:c"]])
 
     assert postprocess_lines(R(), "OUT", 1, True) == opp.lines(R().as_numpy("OUT"), 1, True)
+
+
+@pytest.mark.gpu
+def test_large_output_takes_the_device_route_and_prints_the_same():
+    """More than 256 KB of classification strings: decode and split stay on the device
+    (InferResult.as_device); same lines as the oracle."""
+    from triton_client_b200.image_client import postprocess_lines
+    from triton_client_b200.utils import _small
+
+    rng = np.random.default_rng(9)
+    rows, topk = 4000, 5
+    a = np.empty((rows, topk), dtype=np.object_)
+    for i in range(rows):
+        for j in range(topk):
+            a[i, j] = ("%.6f:%d:class %d of row %d" % (rng.random(), rng.integers(0, 1000), j, i)).encode()
+    res = _response(a)
+    assert len(res._binary_section(res.get_output("OUT"))[0]) > _small.MAX_BYTES
+    assert postprocess_lines(res, "OUT", rows, True) == opp.lines(a, rows, True)

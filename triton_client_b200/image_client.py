@@ -18,7 +18,7 @@ import numpy as np
 
 from . import _lib
 from ._device import current_device, device_buffer, stream_ptr, to_host
-from .utils import triton_to_np_dtype
+from .utils import _small, triton_to_np_dtype
 
 FORMAT_NONE, FORMAT_NHWC, FORMAT_NCHW = 0, 1, 2  # model_config.proto ModelInput.Format
 
@@ -419,7 +419,7 @@ def classification_fields(offsets, payload, device=None):
 
 
 def iter_classification_lines(offsets, payload, device=None):
-    """Yields the lines the reference's postprocess() prints for these elements, in element order:
+    """Iterator over the lines the reference's postprocess() prints for these elements, in element order:
     ``"    {score} ({index}) = {label}"`` with the three fields cut at the element's first three
     ':' and every byte taken as one character (image_client.py:211-216 of the reference joins
     ``chr(x)`` per byte, i.e. Latin-1). An element with fewer than two ':' raises IndexError, as
@@ -427,9 +427,14 @@ def iter_classification_lines(offsets, payload, device=None):
     fields = classification_fields(offsets, payload, device).cpu().numpy()
     n = fields.shape[0]
     if n == 0:
-        return
+        return iter(())
     offs = offsets.cpu().numpy()
     raw = payload[:int(offs[n])].cpu().numpy().tobytes() if int(offs[n]) else b""
+    return _lines_from_host(offs, raw, fields)
+
+
+def _lines_from_host(offs, raw, fields):
+    n = fields.shape[0]
     for b, (f0, f1, f2, ln) in zip(offs[:n].tolist(), fields.tolist()):
         if f1 < 0:
             raise IndexError("list index out of range")
@@ -460,6 +465,13 @@ def _postprocess_iter(results, output_name, batch_size, supports_batching):
     dev = None
     if (shape is not None and out.get("datatype") == "BYTES" and hasattr(results, "as_device")
             and 1 <= len(shape) <= (2 if supports_batching else 1)):
+        section, binary = results._binary_section(out) if hasattr(results, "_binary_section") else (None, False)
+        if binary and 0 < len(section) <= _small.MAX_BYTES:
+            # a few top-k strings: decode + ':' split on one pinned staging buffer (utils/_small.py)
+            if supports_batching and int(shape[0]) != batch_size:
+                raise Exception("expected {} results, got {}".format(batch_size, int(shape[0])))
+            offs, pay, fields = _small.deserialize_stream(section, current_device(), with_fields=True)
+            return _lines_from_host(offs, pay.tobytes(), fields)
         dev = results.as_device(output_name)
     if dev is None:
         output_array = results.as_numpy(output_name)

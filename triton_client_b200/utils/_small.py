@@ -66,7 +66,7 @@ def serialize_objects(pyobj, flat, dev):
         return view[b:b + out_bytes].tobytes()
 
 
-def deserialize_stream(buf, dev):
+def deserialize_stream(buf, dev, with_fields=False):
     """(offsets int64 [n + 1], payload uint8) as numpy copies for the serialized buffer `buf`
     (bytes-like, at most MAX_BYTES), or None when it is too large for this path."""
     nbytes = len(buf)
@@ -92,7 +92,17 @@ def deserialize_stream(buf, dev):
         _lib.check(rc)
         offsets = view[o:o + 8 * (int(n.value) + 1)].view(np.int64).copy()
         payload = view[p:p + int(pb.value)].copy()
-        return offsets, payload
+        if not with_fields:
+            return offsets, payload
+        # classification strings: the ':' split (TcbClassificationFields) on what the decoder just wrote,
+        # still in the stage - a warp per element reads it over PCIe, 32 bytes per round
+        cnt = int(n.value)
+        f = (p + int(pb.value) + 15) & ~15
+        if cnt:
+            _lib.check(_lib.lib.TcbClassificationFields(dev, base + p, base + o, cnt, base + f, s))
+            _lib.check(_lib.lib.TcbStreamSync(dev, s))
+        fields = view[f:f + 32 * cnt].view(np.int64).reshape(cnt, 4).copy()
+        return offsets, payload, fields
 
 
 BF16_MAX_ELEMENTS = 256 << 10  # 1 MiB of float32 in, 512 KiB out: both fit the stage
